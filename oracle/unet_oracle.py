@@ -139,7 +139,7 @@ def mbconv(sd, bn: _BN, x, p: str, b: OBlock, dc):
 
 def unet_forward(sd: dict, x: torch.Tensor, version: str, *, training: bool = True,
                  update_buffers: bool = False, dc_masks=None,
-                 skip_rule: str = "generalised") -> torch.Tensor:
+                 skip_rule: str = "generalised", probe: dict | None = None) -> torch.Tensor:
     """EfficientnetUnet.forward efficientnet_unet.py:125-138 + EfficientNet.encode :251-263.
 
     ``skip_rule="reference"`` keeps the literal ``!= (7, 7)`` test of :259 (tier A: only valid at
@@ -167,18 +167,27 @@ def unet_forward(sd: dict, x: torch.Tensor, version: str, *, training: bool = Tr
     for j, skip in enumerate(maps):                                                 # :129-132
         x = F.conv_transpose2d(x, sd[f"up_convs.{j}.weight"], sd[f"up_convs.{j}.bias"], stride=2)
         x = torch.cat([x, skip], dim=1)
-        x = _double_conv(sd, bn, x, f"double_convs.{j}")
+        x = _double_conv(sd, bn, x, f"double_convs.{j}", probe)
     x = F.conv_transpose2d(x, sd["input_up_conv.weight"], sd["input_up_conv.bias"], stride=2)   # :133-136
     x = torch.cat([x, identity], dim=1)
-    x = _double_conv(sd, bn, x, "input_double_conv")
+    x = _double_conv(sd, bn, x, "input_double_conv", probe)
     return F.conv2d(x, sd["out_conv1x1.weight"], sd["out_conv1x1.bias"])           # :137
 
 
-def _double_conv(sd, bn: _BN, x, p: str):
-    """_double_conv efficientnet_unet.py:168-176: 2x (Conv3x3 p=1 bias -> BN -> ReLU)."""
-    x = F.relu(bn(F.conv2d(x, sd[p + ".0.weight"], sd[p + ".0.bias"], padding=1), p + ".1", BN_MOM_DEC, BN_EPS_DEC))
-    x = F.relu(bn(F.conv2d(x, sd[p + ".3.weight"], sd[p + ".3.bias"], padding=1), p + ".4", BN_MOM_DEC, BN_EPS_DEC))
-    return x
+def _double_conv(sd, bn: _BN, x, p: str, probe: dict | None = None):
+    """_double_conv efficientnet_unet.py:168-176: 2x (Conv3x3 p=1 bias -> BN -> ReLU).
+    ``probe`` (debug aid) records the concat input and the two raw conv outputs with retain_grad()."""
+    def rec(name, t):
+        if probe is not None:
+            if t.requires_grad:
+                t.retain_grad()
+            probe[p + "/" + name] = t
+        return t
+    rec("cat", x)
+    z1 = rec("z1", F.conv2d(x, sd[p + ".0.weight"], sd[p + ".0.bias"], padding=1))
+    x = F.relu(bn(z1, p + ".1", BN_MOM_DEC, BN_EPS_DEC))
+    z2 = rec("z2", F.conv2d(x, sd[p + ".3.weight"], sd[p + ".3.bias"], padding=1))
+    return F.relu(bn(z2, p + ".4", BN_MOM_DEC, BN_EPS_DEC))
 
 
 # --------------------------------------------------------------------------------------------- losses

@@ -1,0 +1,118 @@
+// common.cuh — device helpers shared by all s2lc kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/s2lc.h"
+
+namespace s2lc {
+
+typedef __nv_bfloat16 bf16;
+
+void set_error(const char* fmt, ...);
+int32_t check_launch(const char* what);
+
+#define S2LC_REQUIRE(cond, code, ...)   \
+  do {                                  \
+    if (!(cond)) {                      \
+      s2lc::set_error(__VA_ARGS__);     \
+      return (code);                    \
+    }                                   \
+  } while (0)
+
+constexpr int kNumSMs = 148;
+
+// ------------------------------------------------------------------ scalar load/store by storage type
+template <typename T> __device__ __forceinline__ float ldf(const T* p);
+template <> __device__ __forceinline__ float ldf<float>(const float* p) { return *p; }
+template <> __device__ __forceinline__ float ldf<bf16>(const bf16* p) { return __bfloat162float(*p); }
+template <typename T> __device__ __forceinline__ void stf(T* p, float v);
+template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
+template <> __device__ __forceinline__ void stf<bf16>(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
+// value as it will be read back from storage (used so that statistics see the stored, rounded value)
+template <typename T> __device__ __forceinline__ float roundf_as(float v);
+template <> __device__ __forceinline__ float roundf_as<float>(float v) { return v; }
+template <> __device__ __forceinline__ float roundf_as<bf16>(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+// 8-channel vector access (16 B for bf16, 32 B for fp32); pointers must be 16 B aligned
+template <typename T> struct Vec8;
+template <> struct Vec8<bf16> {
+  static __device__ __forceinline__ void load(const bf16* p, float (&v)[8]) {
+    uint4 u = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 f = __bfloat1622float2(h[i]);
+      v[2 * i] = f.x;
+      v[2 * i + 1] = f.y;
+    }
+  }
+  static __device__ __forceinline__ void store(bf16* p, const float (&v)[8]) {
+    uint4 u;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = u;
+  }
+};
+template <> struct Vec8<float> {
+  static __device__ __forceinline__ void load(const float* p, float (&v)[8]) {
+    float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float (&v)[8]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+};
+
+// ------------------------------------------------------------------ activations
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float act_fwd(float u, int act) {
+  if (act == S2LC_ACT_SILU) return u * sigmoidf_(u);
+  if (act == S2LC_ACT_RELU) return fmaxf(u, 0.f);
+  return u;
+}
+__device__ __forceinline__ float act_bwd(float u, int act) {  // d act(u) / du
+  if (act == S2LC_ACT_SILU) {
+    float s = sigmoidf_(u);
+    return s * (1.f + u * (1.f - s));
+  }
+  if (act == S2LC_ACT_RELU) return u > 0.f ? 1.f : 0.f;
+  return 1.f;
+}
+
+// ------------------------------------------------------------------ lazy sources, element-wise (generic path)
+// value(row, c) of a forward lazy activation; n = sample index of the row, C = channel count (gate row stride)
+template <typename T>
+__device__ __forceinline__ float lazy_at(const s2lc_lazy& L, int64_t row, int c, int n, int C) {
+  float v = ldf<T>(reinterpret_cast<const T*>(L.raw) + row * L.ld + c);
+  if (L.scale) v = v * L.scale[c] + (L.shift ? L.shift[c] : 0.f);
+  v = act_fwd(v, L.act);
+  if (L.gate) v *= L.gate[(int64_t)n * C + c];
+  return v;
+}
+// pre-activation u(row, c) = raw*scale+shift of a lazy activation (for act')
+template <typename T>
+__device__ __forceinline__ float lazy_pre(const s2lc_lazy& L, int64_t row, int c) {
+  float v = ldf<T>(reinterpret_cast<const T*>(L.raw) + row * L.ld + c);
+  if (L.scale) v = v * L.scale[c] + (L.shift ? L.shift[c] : 0.f);
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ float lazygrad_at(const s2lc_lazygrad& G, int64_t row, int c, int n) {
+  float v = ldf<T>(reinterpret_cast<const T*>(G.dy) + row * G.ld_dy + c);
+  if (G.rowscale) v *= G.rowscale[n];
+  if (G.z) v = G.p[c] * v + G.q[c] * ldf<T>(reinterpret_cast<const T*>(G.z) + row * G.ld_z + c) + G.t[c];
+  return v;
+}
+
+// ------------------------------------------------------------------ reductions
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+}  // namespace s2lc

@@ -1,0 +1,834 @@
+// elementwise.cu — library plumbing + the HBM-bound per-pixel / per-channel kernels:
+// BatchNorm finalize/apply/backward-reduce, squeeze-excite, copies, loss, Adam.
+// All activation kernels use 8-channel vectors (16 B bf16 / 32 B fp32) with threads laid out so that
+// consecutive lanes touch consecutive 16 B chunks of an NHWC row (coalesced), and a FIXED channel
+// vector per thread so per-channel reductions stay in registers until one flush per CTA.
+#include <cstdarg>
+#include <cstdio>
+
+#include "common.cuh"
+
+namespace s2lc {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int32_t check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return S2LC_ERR_CUDA;
+  }
+  return S2LC_OK;
+}
+
+// Thread layout for [rows, C] tensors processed in 8-channel vectors.
+struct ChanIter {
+  int cvb;       // channel vectors handled concurrently by a block (<= blockDim)
+  int rows_par;  // rows processed concurrently by a block
+  int c_local, r_local;
+  bool active;
+  __device__ ChanIter(int CV) {
+    cvb = CV < (int)blockDim.x ? CV : (int)blockDim.x;
+    rows_par = blockDim.x / cvb;
+    c_local = threadIdx.x % cvb;
+    r_local = threadIdx.x / cvb;
+    active = r_local < rows_par;
+  }
+};
+
+// Flush per-thread per-channel partials (8 channels x NS stats) to fp64 global accumulators.
+// smem must hold NS * cvb * 8 floats.  stats layout: [NS][C].
+template <int NS>
+__device__ __forceinline__ void flush_stats(float (&acc)[NS][8], const ChanIter& it, int cv0, int C, double* stats,
+                                            float* smem) {
+  const int n = NS * it.cvb * 8;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) smem[i] = 0.f;
+  __syncthreads();
+  if (it.active && cv0 + it.c_local < C / 8) {
+#pragma unroll
+    for (int s = 0; s < NS; ++s)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&smem[(s * it.cvb + it.c_local) * 8 + j], acc[s][j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    int s = i / (it.cvb * 8), r = i % (it.cvb * 8);
+    int c = cv0 * 8 + r;
+    if (c < C) atomicAdd(&stats[(int64_t)s * C + c], (double)smem[i]);
+  }
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------ weight pack
+template <typename T>
+__global__ void weight_pack_kernel(const float* __restrict__ src, T* __restrict__ dst, int N1, int N2, int Tt, int C,
+                                   int Npad, int Cpad, int Kpad, int64_t s1, int64_t s2, int64_t st, int64_t sc,
+                                   int flip) {
+  int64_t total = (int64_t)Npad * Kpad;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int n = (int)(i / Kpad), k = (int)(i % Kpad);
+    int tap = k / Cpad, c = k % Cpad;
+    float v = 0.f;
+    if (n < N1 * N2 && tap < Tt && c < C) {
+      int n1 = n / N2, n2 = n % N2;
+      int tp = flip ? (Tt - 1 - tap) : tap;
+      v = src[n1 * s1 + n2 * s2 + tp * st + c * sc];
+    }
+    stf<T>(dst + i, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ BatchNorm
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, double count, float eps, float momentum,
+                                   float* running_mean, float* running_var, float* scale, float* shift, float* mean_o,
+                                   float* invstd_o, int C) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double mean = stats[c] / count;
+  double var = stats[C + c] / count - mean * mean;
+  if (var < 0) var = 0;
+  double invstd = rsqrt(var + (double)eps);
+  float sc = (float)(gamma[c] * invstd);
+  scale[c] = sc;
+  shift[c] = (float)(beta[c] - mean * gamma[c] * invstd);
+  if (mean_o) mean_o[c] = (float)mean;
+  if (invstd_o) invstd_o[c] = (float)invstd;
+  if (running_mean) {  // torch semantics: running_var uses the unbiased estimator
+    double unbiased = count > 1 ? var * count / (count - 1) : var;
+    running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
+    running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unbiased);
+  }
+}
+
+__global__ void bn_eval_affine_kernel(const float* gamma, const float* beta, const float* rm, const float* rv,
+                                      float eps, float* scale, float* shift, int C) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float inv = rsqrtf(rv[c] + eps);
+  scale[c] = gamma[c] * inv;
+  shift[c] = beta[c] - rm[c] * gamma[c] * inv;
+}
+
+__global__ void bn_bwd_finalize_kernel(const double* __restrict__ stats, const float* __restrict__ mean,
+                                       const float* __restrict__ invstd, const float* __restrict__ gamma, double count,
+                                       float* p, float* q, float* t, float* dgamma, float* dbeta, int C) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  // stats[c] = sum dy, stats[C+c] = sum dy*z  ->  sum dy*zhat = r*(sum dy z - mu*sum dy)
+  double sdy = stats[c], sdyz = stats[C + c];
+  double mu = mean[c], r = invstd[c], g = gamma[c];
+  double sdyzh = r * (sdyz - mu * sdy);
+  double m1 = sdy / count, m2 = sdyzh / count;
+  // dz = g r (dy - m1 - zhat m2),  zhat = (z - mu) r
+  p[c] = (float)(g * r);
+  q[c] = (float)(-g * r * r * m2);
+  t[c] = (float)(g * r * (mu * r * m2 - m1));
+  if (dgamma) dgamma[c] = (float)sdyzh;
+  if (dbeta) dbeta[c] = (float)sdy;
+}
+
+template <typename T>
+__global__ void bn_apply_kernel(s2lc_lazy in, const T* __restrict__ res, int64_t ld_res,
+                                const float* __restrict__ rowscale, T* __restrict__ out, int64_t ld_out, int64_t rows,
+                                int C, int HW) {
+  const int CV = C / 8;
+  ChanIter it(CV);
+  const T* raw = reinterpret_cast<const T*>(in.raw);
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    int cv = cv0 + it.c_local;
+    if (!it.active || cv >= CV) continue;
+    float sc[8], sh[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = in.scale ? in.scale[cv * 8 + j] : 1.f;
+      sh[j] = in.shift ? in.shift[cv * 8 + j] : 0.f;
+    }
+    for (int64_t r = (int64_t)blockIdx.x * it.rows_par + it.r_local; r < rows; r += (int64_t)gridDim.x * it.rows_par) {
+      float v[8];
+      Vec8<T>::load(raw + r * in.ld + cv * 8, v);
+      float rs = rowscale ? rowscale[r / HW] : 1.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j] * sc[j] + sh[j], in.act) * rs;
+      if (res) {
+        float e[8];
+        Vec8<T>::load(res + r * ld_res + cv * 8, e);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] += e[j];
+      }
+      Vec8<T>::store(out + r * ld_out + cv * 8, v);
+    }
+  }
+}
+
+template <typename T>
+__global__ void bn_bwd_reduce_kernel(const T* __restrict__ dy, int64_t ld_dy, const T* __restrict__ z, int64_t ld_z,
+                                     const float* __restrict__ rowscale, double* stats, int64_t rows, int C, int HW) {
+  extern __shared__ float smem[];
+  const int CV = C / 8;
+  ChanIter it(CV);
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    int cv = cv0 + it.c_local;
+    float acc[2][8] = {};
+    if (it.active && cv < CV) {
+      for (int64_t r = (int64_t)blockIdx.x * it.rows_par + it.r_local; r < rows;
+           r += (int64_t)gridDim.x * it.rows_par) {
+        float a[8], b[8];
+        Vec8<T>::load(dy + r * ld_dy + cv * 8, a);
+        Vec8<T>::load(z + r * ld_z + cv * 8, b);
+        float rs = rowscale ? rowscale[r / HW] : 1.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float d = a[j] * rs;
+          acc[0][j] += d;
+          acc[1][j] += d * b[j];
+        }
+      }
+    }
+    flush_stats<2>(acc, it, cv0, C, stats, smem);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ squeeze-excite
+// pooled[n, c] += (1/HW) * sum_{rows of sample n in this split} act(z*scale+shift)
+template <typename T, bool WITH_DA>
+__global__ void se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t ld_da, float* __restrict__ out, int HW,
+                               int C, float mul) {
+  // grid: (splits, N).  WITH_DA: out[n,c] += sum da*act(u)  (d gate), else mean of act(u).
+  const int CV = C / 8;
+  ChanIter it(CV);
+  const int n = blockIdx.y;
+  const T* raw = reinterpret_cast<const T*>(in.raw) + (int64_t)n * HW * in.ld;
+  const T* dap = WITH_DA ? da + (int64_t)n * HW * ld_da : nullptr;
+  extern __shared__ float smem[];
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    int cv = cv0 + it.c_local;
+    float acc[8] = {};
+    if (it.active && cv < CV) {
+      float sc[8], sh[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        sc[j] = in.scale ? in.scale[cv * 8 + j] : 1.f;
+        sh[j] = in.shift ? in.shift[cv * 8 + j] : 0.f;
+      }
+      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += gridDim.x * it.rows_par) {
+        float v[8];
+        Vec8<T>::load(raw + (int64_t)r * in.ld + cv * 8, v);
+        if (WITH_DA) {
+          float d[8];
+          Vec8<T>::load(dap + (int64_t)r * ld_da + cv * 8, d);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += d[j] * act_fwd(v[j] * sc[j] + sh[j], in.act);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += act_fwd(v[j] * sc[j] + sh[j], in.act);
+        }
+      }
+    }
+    // reduce across the rows_par threads that share a channel vector
+    const int nsm = it.cvb * 8;
+    for (int i = threadIdx.x; i < nsm; i += blockDim.x) smem[i] = 0.f;
+    __syncthreads();
+    if (it.active && cv < CV) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&smem[it.c_local * 8 + j], acc[j]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nsm; i += blockDim.x) {
+      int c = cv0 * 8 + i;
+      if (c < C) atomicAdd(&out[(int64_t)n * C + c], smem[i] * mul);
+    }
+    __syncthreads();
+  }
+}
+
+// one block per sample: gate = sigmoid(W2 silu(W1 pooled + b1) + b2)
+__global__ void se_fc_fwd_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
+                                 const float* __restrict__ b1, const float* __restrict__ w2,
+                                 const float* __restrict__ b2, float* __restrict__ gate, int C, int S) {
+  extern __shared__ float smem[];
+  float* xs = smem;      // [C]
+  float* hs = smem + C;  // [S]
+  const int n = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) xs[c] = pooled[(int64_t)n * C + c];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int s = warp; s < S; s += nw) {
+    float a = 0.f;
+    for (int c = lane; c < C; c += 32) a += w1[(int64_t)s * C + c] * xs[c];
+    a = warp_sum(a);
+    if (lane == 0) hs[s] = act_fwd(a + b1[s], S2LC_ACT_SILU);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = b2[c];
+    for (int s = 0; s < S; ++s) a += w2[(int64_t)c * S + s] * hs[s];
+    gate[(int64_t)n * C + c] = sigmoidf_(a);
+  }
+}
+
+// per-sample part of the SE backward: recompute h, gate; write dgp[N,C], h[N,S], dhp[N,S], dpool[N,C]
+__global__ void se_fc_bwd_sample_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
+                                        const float* __restrict__ b1, const float* __restrict__ w2,
+                                        const float* __restrict__ b2, const float* __restrict__ dgate,
+                                        float* __restrict__ dpool, float* __restrict__ sc_dgp,
+                                        float* __restrict__ sc_h, float* __restrict__ sc_dhp, int C, int S) {
+  extern __shared__ float smem[];
+  float* xs = smem;            // [C] pooled
+  float* dg = smem + C;        // [C] dgp
+  float* hp = smem + 2 * C;    // [S] pre-activation
+  float* dh = smem + 2 * C + S;  // [S]
+  const int n = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) xs[c] = pooled[(int64_t)n * C + c];
+  __syncthreads();
+  for (int s = warp; s < S; s += nw) {
+    float a = 0.f;
+    for (int c = lane; c < C; c += 32) a += w1[(int64_t)s * C + c] * xs[c];
+    a = warp_sum(a);
+    if (lane == 0) hp[s] = a + b1[s];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = b2[c];
+    for (int s = 0; s < S; ++s) a += w2[(int64_t)c * S + s] * act_fwd(hp[s], S2LC_ACT_SILU);
+    float g = sigmoidf_(a);
+    float d = dgate[(int64_t)n * C + c] * g * (1.f - g);
+    dg[c] = d;
+    sc_dgp[(int64_t)n * C + c] = d;
+  }
+  __syncthreads();
+  for (int s = warp; s < S; s += nw) {
+    float a = 0.f;
+    for (int c = lane; c < C; c += 32) a += dg[c] * w2[(int64_t)c * S + s];
+    a = warp_sum(a);
+    if (lane == 0) {
+      float d = a * act_bwd(hp[s], S2LC_ACT_SILU);
+      dh[s] = d;
+      sc_dhp[(int64_t)n * S + s] = d;
+      sc_h[(int64_t)n * S + s] = act_fwd(hp[s], S2LC_ACT_SILU);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+    for (int s = 0; s < S; ++s) a += dh[s] * w1[(int64_t)s * C + c];
+    dpool[(int64_t)n * C + c] = a;
+  }
+}
+
+// weight part: dw2[c,s] = sum_n dgp[n,c] h[n,s]; dw1[s,c] = sum_n dhp[n,s] pooled[n,c]; biases
+__global__ void se_fc_bwd_weight_kernel(const float* __restrict__ pooled, const float* __restrict__ sc_dgp,
+                                        const float* __restrict__ sc_h, const float* __restrict__ sc_dhp,
+                                        float* __restrict__ dw1, float* __restrict__ db1, float* __restrict__ dw2,
+                                        float* __restrict__ db2, int N, int C, int S) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= C * S) return;
+  int c = i / S, s = i % S;
+  float a2 = 0.f, a1 = 0.f, bb2 = 0.f, bb1 = 0.f;
+  for (int n = 0; n < N; ++n) {
+    float g = sc_dgp[(int64_t)n * C + c], d = sc_dhp[(int64_t)n * S + s];
+    a2 += g * sc_h[(int64_t)n * S + s];
+    a1 += d * pooled[(int64_t)n * C + c];
+    bb2 += g;
+    bb1 += d;
+  }
+  dw2[(int64_t)c * S + s] = a2;
+  dw1[(int64_t)s * C + c] = a1;
+  if (s == 0) db2[c] = bb2;
+  if (c == 0) db1[s] = bb1;
+}
+
+// da <- (da*gate + dpool/HW) * act'(u), BNBWD stats against z
+template <typename T>
+__global__ void se_bwd_apply_kernel(T* __restrict__ da, int64_t ld_da, s2lc_lazy in, const float* __restrict__ dpool,
+                                    double* stats, int HW, int C, float inv_hw) {
+  extern __shared__ float smem[];
+  const int CV = C / 8;
+  ChanIter it(CV);
+  const int n = blockIdx.y;
+  const T* raw = reinterpret_cast<const T*>(in.raw) + (int64_t)n * HW * in.ld;
+  T* dap = da + (int64_t)n * HW * ld_da;
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    int cv = cv0 + it.c_local;
+    float acc[2][8] = {};
+    if (it.active && cv < CV) {
+      float sc[8], sh[8], g[8], dp[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        int c = cv * 8 + j;
+        sc[j] = in.scale ? in.scale[c] : 1.f;
+        sh[j] = in.shift ? in.shift[c] : 0.f;
+        g[j] = in.gate ? in.gate[(int64_t)n * C + c] : 1.f;
+        dp[j] = dpool ? dpool[(int64_t)n * C + c] * inv_hw : 0.f;
+      }
+      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += gridDim.x * it.rows_par) {
+        float z[8], d[8];
+        Vec8<T>::load(raw + (int64_t)r * in.ld + cv * 8, z);
+        Vec8<T>::load(dap + (int64_t)r * ld_da + cv * 8, d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float u = z[j] * sc[j] + sh[j];
+          float v = roundf_as<T>((d[j] * g[j] + dp[j]) * act_bwd(u, in.act));
+          d[j] = v;
+          acc[0][j] += v;
+          acc[1][j] += v * z[j];
+        }
+        Vec8<T>::store(dap + (int64_t)r * ld_da + cv * 8, d);
+      }
+    }
+    flush_stats<2>(acc, it, cv0, C, stats, smem);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ copies
+template <typename T>
+__global__ void copy_slice_kernel(const T* __restrict__ a, int64_t ld_a, const T* __restrict__ b, int64_t ld_b,
+                                  T* __restrict__ dst, int64_t ld_dst, int64_t rows, int C) {
+  const int CV = C / 8;
+  int64_t total = rows * CV;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / CV;
+    int cv = (int)(i % CV);
+    float v[8];
+    Vec8<T>::load(a + r * ld_a + cv * 8, v);
+    if (b) {
+      float w[8];
+      Vec8<T>::load(b + r * ld_b + cv * 8, w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += w[j];
+    }
+    Vec8<T>::store(dst + r * ld_dst + cv * 8, v);
+  }
+}
+
+template <typename T>
+__global__ void nchw_to_slice_kernel(const float* __restrict__ x, T* __restrict__ dst, int64_t ld_dst, int N, int C,
+                                     int H, int W, int Cfill) {
+  int64_t HW = (int64_t)H * W, total = (int64_t)N * HW;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < total; r += (int64_t)gridDim.x * blockDim.x) {
+    int64_t n = r / HW, hw = r % HW;
+    for (int c = 0; c < Cfill; ++c) {
+      float v = c < C ? x[(n * C + c) * HW + hw] : 0.f;
+      stf<T>(dst + r * ld_dst + c, v);
+    }
+  }
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__global__ void dropconnect_kernel(float* rowscale, int n_blocks, int batch, float rate, uint64_t seed,
+                                   uint64_t step) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_blocks * batch) return;
+  int b = i / batch;
+  float keep = 1.f - rate * ((float)b / (float)n_blocks);
+  uint64_t h = splitmix64(splitmix64(seed ^ (step * 0xD1B54A32D192ED03ull)) + (uint64_t)i);
+  float u = (float)(h >> 40) * (1.0f / 16777216.0f);  // [0,1)
+  rowscale[i] = floorf(keep + u) / keep;
+}
+
+// ------------------------------------------------------------------------------------------ loss
+// FocalLoss.__call__ (reference src/losses.py:77-89) and weighted nn.CrossEntropyLoss (:36-40), forward value and
+// d(loss)/d(logits) in one pass over the logits.  One thread per pixel; logits row = CLS contiguous values.
+template <typename T, int CLS>
+__global__ void loss_kernel(const T* __restrict__ logits, int64_t ld, const int64_t* __restrict__ y,
+                            const float* __restrict__ cw, float gamma, float ls, int64_t ignore_index, int kind,
+                            float out_scale_const, const float* __restrict__ wsum, float* __restrict__ loss_out,
+                            T* __restrict__ dlogits, int64_t ld_d, int64_t rows) {
+  float w[CLS];
+  float wtot = 0.f;
+#pragma unroll
+  for (int c = 0; c < CLS; ++c) {
+    w[c] = cw ? cw[c] : 1.f;
+    wtot += w[c];
+  }
+  // mean-reduction scale: focal -> 1/rows (ALL pixels, losses.py:131-134); CE -> 1/sum of target weights
+  float scale = out_scale_const;
+  if (wsum) scale = 1.f / fmaxf(*wsum, 1e-30f);
+  float local = 0.f;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
+    float z[CLS];
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) z[c] = ldf<T>(logits + r * ld + c);
+    int64_t t = y[r];
+    float d[CLS];
+    bool ign = (t == ignore_index) || t < 0 || t >= CLS;
+    if (ign) {
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) d[c] = 0.f;
+    } else {
+      float m = z[0];
+#pragma unroll
+      for (int c = 1; c < CLS; ++c) m = fmaxf(m, z[c]);
+      float se = 0.f;
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) se += expf(z[c] - m);
+      float lse = m + logf(se);
+      float p[CLS], lp_t = 0.f, p_sum_neg_lp = 0.f, w_t = 0.f, wlp = 0.f;
+#pragma unroll
+      for (int c = 0; c < CLS; ++c) {
+        float lp = z[c] - lse;
+        p[c] = expf(lp);
+        p_sum_neg_lp -= lp;
+        wlp -= w[c] * lp;
+        if (c == (int)t) {
+          lp_t = lp;
+          w_t = w[c];
+        }
+      }
+      if (kind == S2LC_LOSS_FOCAL) {
+        // ce (unweighted, label-smoothed) -> pt = exp(-ce) -> alpha_t (1-pt)^gamma ce
+        float ce = (1.f - ls) * (-lp_t) + (ls / CLS) * p_sum_neg_lp;
+        float pt = expf(-ce);
+        float om = fmaxf(1.f - pt, 0.f);
+        float f = powf(om, gamma);
+        float fl = w_t * f * ce;
+        // d fl / d ce = alpha [ (1-pt)^g + g (1-pt)^(g-1) pt ce ]
+        float fm1 = (gamma == 0.f) ? 0.f : (om > 0.f ? gamma * powf(om, gamma - 1.f) : (gamma == 1.f ? 1.f : 0.f));
+        float dfl = w_t * (f + fm1 * pt * ce);
+        local += fl;
+#pragma unroll
+        for (int c = 0; c < CLS; ++c) d[c] = dfl * (p[c] - (c == (int)t ? (1.f - ls) : 0.f) - ls / CLS) * scale;
+      } else {
+        float li = (1.f - ls) * w_t * (-lp_t) + (ls / CLS) * wlp;
+        local += li;
+#pragma unroll
+        for (int c = 0; c < CLS; ++c)
+          d[c] = ((1.f - ls) * w_t * (p[c] - (c == (int)t ? 1.f : 0.f)) + (ls / CLS) * (p[c] * wtot - w[c])) * scale;
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < CLS; ++c) stf<T>(dlogits + r * ld_d + c, d[c]);
+  }
+  local = warp_sum(local);
+  __shared__ float part[32];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) atomicAdd(loss_out, v * scale);
+  }
+}
+
+// sum of class weights of the non-ignored targets (denominator of the weighted CE mean)
+__global__ void loss_wsum_kernel(const int64_t* __restrict__ y, const float* __restrict__ cw, int64_t ignore_index,
+                                 int cls, float* wsum, int64_t rows) {
+  float local = 0.f;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
+    int64_t t = y[r];
+    if (t != ignore_index && t >= 0 && t < cls) local += cw ? cw[t] : 1.f;
+  }
+  local = warp_sum(local);
+  __shared__ float part[32];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) atomicAdd(wsum, v);
+  }
+}
+
+template <typename T>
+__global__ void scale_inplace_kernel(T* x, int64_t ld, const float* factor, int64_t rows, int C) {
+  float f = *factor;
+  int64_t total = rows * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    T* p = x + (i / C) * ld + (i % C);
+    stf<T>(p, ldf<T>(p) * f);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ Adam (L2 decay)
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps, float wd,
+                            float bc1, float bc2_sqrt, float gscale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float pi = p[i];
+    float gi = g[i] * gscale + wd * pi;
+    float mi = b1 * m[i] + (1.f - b1) * gi;
+    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = pi - (lr / bc1) * (mi / denom);
+  }
+}
+
+static inline int grid_for(int64_t work_items, int per_block, int max_blocks = kNumSMs * 8) {
+  int64_t b = (work_items + per_block - 1) / per_block;
+  if (b < 1) b = 1;
+  if (b > max_blocks) b = max_blocks;
+  return (int)b;
+}
+
+}  // namespace s2lc
+
+using namespace s2lc;
+
+#define DISPATCH_T(dtype, ...)                                   \
+  if ((dtype) == S2LC_F32) {                                     \
+    typedef float T;                                             \
+    __VA_ARGS__;                                                 \
+  } else if ((dtype) == S2LC_BF16) {                             \
+    typedef s2lc::bf16 T;                                        \
+    __VA_ARGS__;                                                 \
+  } else {                                                       \
+    s2lc::set_error("bad dtype %d", (int)(dtype));               \
+    return S2LC_ERR_SHAPE;                                       \
+  }
+
+template <typename T>
+static int32_t launch_loss(const void* logits, int64_t ld, const int64_t* y, const float* cw, float gamma, float ls,
+                           int64_t ii, int kind, float scale, const float* wsum, float* loss_out, void* dl,
+                           int64_t ld_d, int64_t rows, int cls, cudaStream_t st) {
+  int grid = grid_for(rows, 256, kNumSMs * 8);
+#define L(CLS)                                                                                                       \
+  case CLS:                                                                                                          \
+    loss_kernel<T, CLS><<<grid, 256, 0, st>>>((const T*)logits, ld, y, cw, gamma, ls, ii, kind, scale, wsum, loss_out, \
+                                              (T*)dl, ld_d, rows);                                                    \
+    break;
+  switch (cls) {
+    L(2) L(3) L(4) L(5) L(6) L(7) L(8)
+    default:
+      set_error("loss: n_classes=%d unsupported (2..8)", cls);
+      return S2LC_ERR_SHAPE;
+  }
+#undef L
+  return check_launch("loss_fwd_bwd");
+}
+
+extern "C" {
+
+int32_t s2lc_version(void) { return 100; }
+const char* s2lc_last_error(void) { return s2lc::g_err; }
+
+int32_t s2lc_arch_check(int32_t device) {
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) {
+    set_error("cudaGetDeviceProperties(%d): %s", device, cudaGetErrorString(e));
+    return S2LC_ERR_CUDA;
+  }
+  S2LC_REQUIRE(prop.major == 10, S2LC_ERR_ARCH, "libs2lc is built for sm_100a only; device %d is sm_%d%d", device,
+               prop.major, prop.minor);
+  return S2LC_OK;
+}
+
+int32_t s2lc_memset_zero(void* ptr, int64_t bytes, void* stream) {
+  cudaError_t e = cudaMemsetAsync(ptr, 0, (size_t)bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    set_error("cudaMemsetAsync: %s", cudaGetErrorString(e));
+    return S2LC_ERR_CUDA;
+  }
+  return S2LC_OK;
+}
+
+int32_t s2lc_weight_pack(const float* src, void* dst, int32_t dtype, int32_t N1, int32_t N2, int32_t T_, int32_t C,
+                         int32_t Npad, int32_t Cpad, int32_t Kpad, int64_t s1, int64_t s2, int64_t st, int64_t sc,
+                         int32_t flip, void* stream) {
+  S2LC_REQUIRE(Npad >= N1 * N2 && Cpad >= C && Kpad >= T_ * Cpad, S2LC_ERR_SHAPE, "weight_pack: bad padding");
+  int64_t total = (int64_t)Npad * Kpad;
+  DISPATCH_T(dtype, (weight_pack_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+                        src, (T*)dst, N1, N2, T_, C, Npad, Cpad, Kpad, s1, s2, st, sc, flip)));
+  return check_launch("weight_pack");
+}
+
+int32_t s2lc_bn_finalize(const double* stats, const float* gamma, const float* beta, double count, float eps,
+                         float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                         float* mean, float* invstd, int32_t C, void* stream) {
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, gamma, beta, count, eps, momentum,
+                                                                         running_mean, running_var, scale, shift,
+                                                                         mean, invstd, C);
+  return check_launch("bn_finalize");
+}
+
+int32_t s2lc_bn_eval_affine(const float* gamma, const float* beta, const float* running_mean,
+                            const float* running_var, float eps, float* scale, float* shift, int32_t C,
+                            void* stream) {
+  bn_eval_affine_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var,
+                                                                            eps, scale, shift, C);
+  return check_launch("bn_eval_affine");
+}
+
+int32_t s2lc_bn_bwd_finalize(const double* stats, const float* mean, const float* invstd, const float* gamma,
+                             double count, float* p, float* q, float* t, float* dgamma, float* dbeta, int32_t C,
+                             void* stream) {
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, mean, invstd, gamma, count, p, q,
+                                                                             t, dgamma, dbeta, C);
+  return check_launch("bn_bwd_finalize");
+}
+
+int32_t s2lc_bn_apply(const s2lc_lazy* in, const void* residual, int64_t ld_res, const float* rowscale, void* out,
+                      int64_t ld_out, int64_t rows, int32_t C, int32_t HW, int32_t dtype, void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_out % 8 == 0 && (!residual || ld_res % 8 == 0), S2LC_ERR_ALIGN,
+               "bn_apply: C and strides must be multiples of 8 (C=%d)", C);
+  DISPATCH_T(dtype, (bn_apply_kernel<T><<<grid_for(rows * (C / 8), 256 * 4), 256, 0, (cudaStream_t)stream>>>(
+                        *in, (const T*)residual, ld_res, rowscale, (T*)out, ld_out, rows, C, HW)));
+  return check_launch("bn_apply");
+}
+
+static inline size_t stats_smem(int C, int ns) {
+  int cvb = C / 8 < 256 ? C / 8 : 256;
+  return (size_t)ns * cvb * 8 * sizeof(float);
+}
+
+int32_t s2lc_bn_bwd_reduce(const void* dy, int64_t ld_dy, const void* z, int64_t ld_z, const float* rowscale,
+                           double* stats, int64_t rows, int32_t C, int32_t HW, int32_t dtype, void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && ld_dy % 8 == 0 && ld_z % 8 == 0, S2LC_ERR_ALIGN, "bn_bwd_reduce: alignment (C=%d)", C);
+  DISPATCH_T(dtype, (bn_bwd_reduce_kernel<T><<<grid_for(rows * (C / 8), 256 * 8, kNumSMs * 4), 256, stats_smem(C, 2),
+                                               (cudaStream_t)stream>>>((const T*)dy, ld_dy, (const T*)z, ld_z,
+                                                                       rowscale, stats, rows, C, HW)));
+  return check_launch("bn_bwd_reduce");
+}
+
+static inline int se_splits(int N, int HW, int C) {
+  int cvb = C / 8 < 256 ? C / 8 : 256;
+  int rows_par = 256 / cvb;
+  int want = (kNumSMs * 4 + N - 1) / N;
+  int maxs = (HW + rows_par * 4 - 1) / (rows_par * 4);
+  int s = want < maxs ? want : maxs;
+  return s < 1 ? 1 : s;
+}
+
+int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, int32_t C, int32_t dtype,
+                     void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0, S2LC_ERR_ALIGN, "se_pool: alignment (C=%d)", C);
+  cudaMemsetAsync(pooled, 0, sizeof(float) * (size_t)N * C, (cudaStream_t)stream);
+  dim3 grid(se_splits(N, HW, C), N);
+  DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, 256, stats_smem(C, 1), (cudaStream_t)stream>>>(
+                        *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW)));
+  return check_launch("se_pool");
+}
+
+int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, float* dgate, int32_t N, int32_t HW,
+                           int32_t C, int32_t dtype, void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_da % 8 == 0, S2LC_ERR_ALIGN, "se_bwd_reduce: alignment (C=%d)", C);
+  cudaMemsetAsync(dgate, 0, sizeof(float) * (size_t)N * C, (cudaStream_t)stream);
+  dim3 grid(se_splits(N, HW, C), N);
+  DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, 256, stats_smem(C, 1), (cudaStream_t)stream>>>(
+                        *in, (const T*)da, ld_da, dgate, HW, C, 1.f)));
+  return check_launch("se_bwd_reduce");
+}
+
+int32_t s2lc_se_fc_fwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
+                       float* gate, int32_t N, int32_t C, int32_t S, void* stream) {
+  size_t smem = sizeof(float) * (size_t)(C + S);
+  se_fc_fwd_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(pooled, w1, b1, w2, b2, gate, C, S);
+  return check_launch("se_fc_fwd");
+}
+
+int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
+                       const float* dgate, float* dpool, float* dw1, float* db1, float* dw2, float* db2,
+                       float* scratch, int32_t N, int32_t C, int32_t S, void* stream) {
+  float* sc_dgp = scratch;
+  float* sc_h = scratch + (size_t)N * C;
+  float* sc_dhp = sc_h + (size_t)N * S;
+  size_t smem = sizeof(float) * (size_t)(2 * C + 2 * S);
+  se_fc_bwd_sample_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(pooled, w1, b1, w2, b2, dgate, dpool, sc_dgp, sc_h,
+                                                                   sc_dhp, C, S);
+  se_fc_bwd_weight_kernel<<<(C * S + 255) / 256, 256, 0, (cudaStream_t)stream>>>(pooled, sc_dgp, sc_h, sc_dhp, dw1,
+                                                                                  db1, dw2, db2, N, C, S);
+  return check_launch("se_fc_bwd");
+}
+
+int32_t s2lc_se_bwd_apply(void* da, int64_t ld_da, const s2lc_lazy* in, const float* dpool, double* stats, int32_t N,
+                          int32_t HW, int32_t C, int32_t dtype, void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_da % 8 == 0, S2LC_ERR_ALIGN, "se_bwd_apply: alignment (C=%d)", C);
+  dim3 grid(se_splits(N, HW, C), N);
+  DISPATCH_T(dtype, (se_bwd_apply_kernel<T><<<grid, 256, stats_smem(C, 2), (cudaStream_t)stream>>>(
+                        (T*)da, ld_da, *in, dpool, stats, HW, C, 1.f / (float)HW)));
+  return check_launch("se_bwd_apply");
+}
+
+int32_t s2lc_copy_slice(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int64_t rows, int32_t C,
+                        int32_t dtype, void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && ld_src % 8 == 0 && ld_dst % 8 == 0, S2LC_ERR_ALIGN, "copy_slice: alignment (C=%d)", C);
+  DISPATCH_T(dtype, (copy_slice_kernel<T><<<grid_for(rows * (C / 8), 256 * 2), 256, 0, (cudaStream_t)stream>>>(
+                        (const T*)src, ld_src, nullptr, 0, (T*)dst, ld_dst, rows, C)));
+  return check_launch("copy_slice");
+}
+
+int32_t s2lc_add_slice(const void* a, int64_t ld_a, const void* b, int64_t ld_b, void* dst, int64_t ld_dst,
+                       int64_t rows, int32_t C, int32_t dtype, void* stream) {
+  S2LC_REQUIRE(C % 8 == 0 && ld_a % 8 == 0 && ld_b % 8 == 0 && ld_dst % 8 == 0, S2LC_ERR_ALIGN,
+               "add_slice: alignment (C=%d)", C);
+  DISPATCH_T(dtype, (copy_slice_kernel<T><<<grid_for(rows * (C / 8), 256 * 2), 256, 0, (cudaStream_t)stream>>>(
+                        (const T*)a, ld_a, (const T*)b, ld_b, (T*)dst, ld_dst, rows, C)));
+  return check_launch("add_slice");
+}
+
+int32_t s2lc_nchw_to_slice(const float* x_nchw, void* dst, int64_t ld_dst, int32_t N, int32_t C, int32_t H, int32_t W,
+                           int32_t Cfill, int32_t dtype, void* stream) {
+  int64_t rows = (int64_t)N * H * W;
+  DISPATCH_T(dtype, (nchw_to_slice_kernel<T><<<grid_for(rows, 256), 256, 0, (cudaStream_t)stream>>>(
+                        x_nchw, (T*)dst, ld_dst, N, C, H, W, Cfill)));
+  return check_launch("nchw_to_slice");
+}
+
+int32_t s2lc_dropconnect_masks(float* rowscale, int32_t n_blocks, int32_t batch, float rate, uint64_t seed,
+                               uint64_t step, void* stream) {
+  int n = n_blocks * batch;
+  dropconnect_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(rowscale, n_blocks, batch, rate, seed, step);
+  return check_launch("dropconnect_masks");
+}
+
+int32_t s2lc_loss_fwd_bwd(const void* logits, int64_t ld, const int64_t* y, const float* class_w, float gamma,
+                          float label_smoothing, int64_t ignore_index, int32_t kind, int32_t reduce_mean,
+                          float* loss_out, float* wsum_scratch, void* dlogits, int64_t ld_d, int64_t rows,
+                          int32_t n_classes, int32_t dtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(loss_out, 0, sizeof(float), st);
+  float scale = 1.f;
+  const float* wsum = nullptr;
+  if (reduce_mean) {
+    if (kind == S2LC_LOSS_FOCAL) {
+      scale = 1.f / (float)rows;
+    } else {
+      S2LC_REQUIRE(wsum_scratch != nullptr, S2LC_ERR_SHAPE, "loss: CE mean needs wsum_scratch");
+      cudaMemsetAsync(wsum_scratch, 0, sizeof(float), st);
+      loss_wsum_kernel<<<grid_for(rows, 256, kNumSMs * 8), 256, 0, st>>>(y, class_w, ignore_index, n_classes,
+                                                                         wsum_scratch, rows);
+      wsum = wsum_scratch;
+    }
+  }
+  if (dtype == S2LC_F32)
+    return launch_loss<float>(logits, ld, y, class_w, gamma, label_smoothing, ignore_index, kind, scale, wsum,
+                              loss_out, dlogits, ld_d, rows, n_classes, st);
+  if (dtype == S2LC_BF16)
+    return launch_loss<s2lc::bf16>(logits, ld, y, class_w, gamma, label_smoothing, ignore_index, kind, scale, wsum,
+                                   loss_out, dlogits, ld_d, rows, n_classes, st);
+  set_error("bad dtype %d", dtype);
+  return S2LC_ERR_SHAPE;
+}
+
+int32_t s2lc_scale_inplace(void* x, int64_t ld, const float* factor_dev, int64_t rows, int32_t C, int32_t dtype,
+                           void* stream) {
+  DISPATCH_T(dtype, (scale_inplace_kernel<T><<<grid_for(rows * C, 256 * 4), 256, 0, (cudaStream_t)stream>>>(
+                        (T*)x, ld, factor_dev, rows, C)));
+  return check_launch("scale_inplace");
+}
+
+int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                       float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+                       void* stream) {
+  double bc1 = 1.0 - pow((double)beta1, (double)step);
+  double bc2 = 1.0 - pow((double)beta2, (double)step);
+  adam_kernel<<<grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
+                                                                      beta2, eps, weight_decay, (float)bc1,
+                                                                      (float)sqrt(bc2), grad_scale);
+  return check_launch("adam_step");
+}
+
+}  // extern "C"

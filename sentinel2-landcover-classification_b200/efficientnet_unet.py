@@ -1,0 +1,245 @@
+"""EfficientNet-UNet with the reference's constructor / forward / state_dict contract, executed by
+hand-written sm_100a CUDA kernels through the libs2lc C ABI.
+
+Mirrors ``src/modules/efficientnet_unet.py`` of MaxWolf-01/sentinel2-landcover-classification:
+``EfficientNetConfig`` (:18-53), ``EfficientnetUnet(config, concat_input=True)`` (:106-123) with
+``forward(x[B,C,H,W]) -> logits[B,num_classes,H,W]`` (:125-138).  The module tree only HOLDS the
+parameters and buffers (so ``state_dict()`` has exactly the reference's keys and shapes); all compute
+goes through ``_engine.Engine``: a launch list of libs2lc kernels (forward) and its hand-written
+reverse pass (backward) wrapped in ONE ``torch.autograd.Function``.
+
+Deliberate, declared differences from the reference:
+  * skip selection uses the generalised rule of SURVEY.md F1 (drop the map whose HxW equals the
+    head's) — bit-identical to the reference's literal ``(7, 7)`` at 224x224, and the only way the
+    512x512 / 1024x1024 configs of BASELINE.json can run at all;
+  * drop-connect draws come from a counter-based generator inside the library (or can be injected
+    with ``set_drop_connect_masks``), not from torch's global Philox stream;
+  * there is no CPU path: a CPU tensor raises.
+"""
+from __future__ import annotations
+
+import math
+import typing
+from dataclasses import dataclass
+
+import torch
+from torch import nn
+
+__all__ = ["EfficientNetConfig", "EfficientnetUnet", "BlockSpec", "architecture"]
+
+_VERSIONS = {  # (width, depth, dropout) — reference :35-46
+    "b0": (1.0, 1.0, 0.2), "b1": (1.0, 1.1, 0.2), "b2": (1.1, 1.2, 0.3), "b3": (1.2, 1.4, 0.3),
+    "b4": (1.4, 1.8, 0.4), "b5": (1.6, 2.2, 0.4), "b6": (1.8, 2.6, 0.5), "b7": (2.0, 3.1, 0.5),
+}
+# stage table of EfficientNet (reference :201-209): repeats, kernel, stride, expand, in, out
+_STAGE_TABLE = ((1, 3, 1, 1, 32, 16), (2, 3, 2, 6, 16, 24), (2, 5, 2, 6, 24, 40), (3, 3, 2, 6, 40, 80),
+                (3, 5, 1, 6, 80, 112), (4, 5, 2, 6, 112, 192), (1, 3, 1, 6, 192, 320))
+_HEAD_CHANNELS = {"b0": 1280, "b1": 1280, "b2": 1408, "b3": 1536, "b4": 1792, "b5": 2048, "b6": 2304, "b7": 2560}
+_CAT_WIDTHS = {"b0": (592, 296, 152, 80, 38, 32), "b1": (592, 296, 152, 80, 38, 32), "b2": (600, 304, 152, 80, 38, 32),
+               "b3": (608, 304, 160, 88, 38, 32), "b4": (624, 312, 160, 88, 38, 32), "b5": (640, 320, 168, 88, 38, 32),
+               "b6": (656, 328, 168, 96, 38, 32), "b7": (672, 336, 176, 96, 38, 32)}
+
+
+@dataclass
+class EfficientNetConfig:
+    """Same fields and semantics as the reference dataclass (:18-53), including the ``bn_momentum`` flip."""
+    version: typing.Literal["b0", "b1", "b2", "b3", "b4", "b5", "b6", "b7"]
+    in_channels: int
+    num_classes: int
+    bn_momentum: float = 0.99
+    bn_epsilon: float = 1e-3
+    depth_divisor: int | None = 8
+    drop_connect_rate: float | None = 0.2
+    min_depth: int | None = None
+    class_distribution: list[float] | None = None
+    dropout_rate: float | None = None
+    width_coefficient: float | None = None
+    depth_coefficient: float | None = None
+
+    def __post_init__(self) -> None:
+        if self.version not in _VERSIONS:
+            raise ValueError(f"There is no model version {self.version}")
+        w, d, p = _VERSIONS[self.version]
+        self.width_coefficient = self.width_coefficient or w
+        self.depth_coefficient = self.depth_coefficient or d
+        self.dropout_rate = self.dropout_rate or p
+        self.bn_momentum = 1 - self.bn_momentum
+
+
+@dataclass(frozen=True)
+class BlockSpec:
+    index: int
+    kernel: int
+    stride: int
+    c_in: int
+    c_exp: int
+    c_out: int
+    c_se: int
+    expand: bool
+    residual: bool
+
+
+def _scaled_width(filters: int, cfg: EfficientNetConfig) -> int:
+    if cfg.width_coefficient is None:
+        return filters
+    div = cfg.depth_divisor
+    scaled = filters * cfg.width_coefficient
+    floor_ = cfg.min_depth or div
+    snapped = max(floor_, int(scaled + div / 2) // div * div)
+    if snapped < 0.9 * scaled:
+        snapped += div
+    return int(snapped)
+
+
+def architecture(cfg: EfficientNetConfig) -> tuple[int, list[BlockSpec], int]:
+    """(stem channels, MBConv block list, head channels) for ``cfg`` (reference :184-228, :303-375)."""
+    blocks: list[BlockSpec] = []
+    for reps, k, s, e, fi, fo in _STAGE_TABLE:
+        ci, co = _scaled_width(fi, cfg), _scaled_width(fo, cfg)
+        n = int(math.ceil(cfg.depth_coefficient * reps)) if cfg.depth_coefficient is not None else reps
+        for j in range(n):
+            c_in, stride = (ci, s) if j == 0 else (co, 1)
+            blocks.append(BlockSpec(index=len(blocks), kernel=k, stride=stride, c_in=c_in, c_exp=c_in * e, c_out=co,
+                                    c_se=max(1, int(c_in * 0.25)), expand=e != 1,
+                                    residual=stride == 1 and c_in == co))
+    return _scaled_width(32, cfg), blocks, _scaled_width(1280, cfg)
+
+
+# --------------------------------------------------------------------------------------------------
+# Parameter containers.  Stock torch modules are used ONLY as holders so the state_dict key layout
+# (Sequential indices included) is the reference's; their forward() is never called.
+def _bn(c: int, cfg: EfficientNetConfig | None) -> nn.BatchNorm2d:
+    if cfg is None:
+        return nn.BatchNorm2d(c)  # decoder: torch defaults eps=1e-5, momentum=0.1 (reference :171,:174)
+    return nn.BatchNorm2d(c, momentum=cfg.bn_momentum, eps=cfg.bn_epsilon)
+
+
+class _MBConvParams(nn.Module):
+    def __init__(self, spec: BlockSpec, cfg: EfficientNetConfig) -> None:
+        super().__init__()
+        self.spec = spec
+        layers: list[nn.Module] = []
+        if spec.expand:
+            layers += [nn.Conv2d(spec.c_in, spec.c_exp, 1, bias=False), _bn(spec.c_exp, cfg), nn.Identity()]
+        layers += [nn.Conv2d(spec.c_exp, spec.c_exp, spec.kernel, stride=spec.stride, groups=spec.c_exp, bias=False),
+                   _bn(spec.c_exp, cfg), nn.Identity()]
+        self.stem = nn.Sequential(*layers)
+        self.squeeze_excitation = nn.Sequential(nn.Identity(), nn.Conv2d(spec.c_exp, spec.c_se, 1), nn.Identity(),
+                                                nn.Conv2d(spec.c_se, spec.c_exp, 1))
+        self.final_layer = nn.Sequential(nn.Conv2d(spec.c_exp, spec.c_out, 1, bias=False), _bn(spec.c_out, cfg))
+
+
+class _EncoderParams(nn.Module):
+    def __init__(self, cfg: EfficientNetConfig) -> None:
+        super().__init__()
+        stem_c, specs, head_c = architecture(cfg)
+        self.name = cfg.version
+        self.drop_connect_rate = cfg.drop_connect_rate
+        self.specs = specs
+        self.stem = nn.Sequential(nn.Conv2d(cfg.in_channels, stem_c, 3, stride=2, bias=False), _bn(stem_c, cfg),
+                                  nn.Identity())
+        self.blocks = nn.ModuleList([_MBConvParams(s, cfg) for s in specs])
+        self.conv_head = nn.Sequential(nn.Conv2d(specs[-1].c_out, head_c, 1, bias=False), _bn(head_c, cfg),
+                                       nn.Identity())
+        # classification head of the plain EfficientNet: built (state_dict parity) but unused by the UNet (F5)
+        self.fc = nn.Sequential(nn.Identity(), nn.Identity(), nn.Identity(), nn.Linear(head_c, cfg.num_classes))
+
+
+def _double_conv_params(c_in: int, c_out: int) -> nn.Sequential:
+    return nn.Sequential(nn.Conv2d(c_in, c_out, 3, padding=1), _bn(c_out, None), nn.Identity(),
+                         nn.Conv2d(c_out, c_out, 3, padding=1), _bn(c_out, None), nn.Identity())
+
+
+def _init_like_reference(root: nn.Module) -> None:
+    """kaiming-normal(fan_out, relu) convs, zero biases, BN 1/0, xavier Linear — reference :401-412."""
+    for m in root.modules():
+        if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+            nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+            if m.bias is not None:
+                nn.init.zeros_(m.bias)
+        elif isinstance(m, nn.BatchNorm2d):
+            nn.init.ones_(m.weight)
+            nn.init.zeros_(m.bias)
+        elif isinstance(m, nn.Linear):
+            nn.init.xavier_normal_(m.weight)
+            nn.init.zeros_(m.bias)
+
+
+class EfficientnetUnet(nn.Module):
+    """Drop-in for the reference class of the same name (constructor :107, forward :125)."""
+
+    def __init__(self, config: EfficientNetConfig, concat_input: bool = True) -> None:
+        super().__init__()
+        if not concat_input:
+            raise NotImplementedError("concat_input=False is not used anywhere in the reference and is not built")
+        self.config = config
+        self.encoder = _EncoderParams(config)
+        head_c = _HEAD_CHANNELS[config.version]
+        cat = _CAT_WIDTHS[config.version]
+        ups_in = [head_c, 512, 256, 128]
+        ups_out = [512, 256, 128, 64]
+        self.up_convs = nn.ModuleList([nn.ConvTranspose2d(i, o, kernel_size=2, stride=2) for i, o in zip(ups_in, ups_out)])
+        self.double_convs = nn.ModuleList([_double_conv_params(c, o) for c, o in zip(cat[:4], ups_out)])
+        self.concat_input = concat_input
+        self.input_up_conv = nn.ConvTranspose2d(64, 32, kernel_size=2, stride=2)
+        self.input_double_conv = _double_conv_params(cat[4], 32)
+        self.out_conv1x1 = nn.Conv2d(cat[5], config.num_classes, kernel_size=1)
+        _init_like_reference(self)
+        if config.class_distribution is not None:  # reference src/utils.py:174-188
+            dist = torch.tensor(config.class_distribution, dtype=torch.float32) + 1e-6
+            if len(dist) == 2:
+                self.out_conv1x1.bias.data.fill_(float((dist[1] / dist[0]).log()))
+            else:
+                self.out_conv1x1.bias.data = dist.log()
+        self.precision: str = "auto"       # "auto": bf16 under torch.autocast(bf16) else fp32; or "bf16" / "fp32"
+        self._engine = None
+        self._dc_masks = None
+        self._dc_step = 0
+
+    # ------------------------------------------------------------------ reference-shaped helpers
+    @property
+    def n_channels(self) -> int:
+        return _HEAD_CHANNELS[self.encoder.name]
+
+    @property
+    def size(self) -> tuple[int, ...]:
+        return _CAT_WIDTHS[self.encoder.name]
+
+    def set_precision(self, precision: str) -> "EfficientnetUnet":
+        assert precision in ("auto", "bf16", "fp32")
+        self.precision = precision
+        return self
+
+    def set_drop_connect_masks(self, masks: torch.Tensor | None) -> None:
+        """Inject per-block, per-sample drop-connect factors [n_blocks, B] (already divided by keep).  Used by the
+        parity tests, which cannot reproduce torch's global RNG stream; ``None`` returns to the internal generator."""
+        self._dc_masks = masks
+
+    def used_parameters(self) -> list[tuple[str, nn.Parameter]]:
+        """Parameters that receive a gradient in the UNet forward (everything but encoder.fc.3.*)."""
+        return [(k, p) for k, p in self.named_parameters() if not k.startswith("encoder.fc.")]
+
+    def _compute_dtype(self) -> torch.dtype:
+        if self.precision == "bf16":
+            return torch.bfloat16
+        if self.precision == "fp32":
+            return torch.float32
+        if torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16:
+            return torch.bfloat16
+        return torch.float32
+
+    def engine(self):
+        if self._engine is None:
+            from ._engine import Engine
+            self._engine = Engine(self)
+        return self._engine
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda:
+            raise RuntimeError("s2lc EfficientnetUnet runs on sm_100a CUDA devices only (no CPU fallback)")
+        if x.dim() != 4 or x.shape[1] != self.config.in_channels:
+            raise ValueError(f"expected [B, {self.config.in_channels}, H, W], got {tuple(x.shape)}")
+        if x.shape[2] % 32 or x.shape[3] % 32:
+            raise ValueError("H and W must be multiples of 32 (5 stride-2 stages; the reference fails otherwise too)")
+        from ._engine import unet_apply
+        return unet_apply(self, x, self._compute_dtype())

@@ -1,0 +1,79 @@
+"""Shared helpers for the model-level parity tests: run the oracle and the CUDA path on identical synthetic data."""
+from __future__ import annotations
+
+import torch
+
+from oracle import unet_oracle as O
+from s2lc_b200 import synthetic
+from s2lc_b200.efficientnet_unet import EfficientNetConfig, EfficientnetUnet
+from s2lc_b200.losses import CrossEntropyLoss, FocalLoss
+
+
+def alpha_weights() -> torch.Tensor:
+    return O.loss_class_weights(list(synthetic.CLASS_DISTRIBUTION), masked_loss=True)
+
+
+def build_model(version: str, precision: str, dc_rate=None, seed: int = 0):
+    cfg = EfficientNetConfig(version=version, in_channels=6, num_classes=4, drop_connect_rate=dc_rate,
+                             class_distribution=list(synthetic.CLASS_DISTRIBUTION))
+    model = EfficientnetUnet(cfg)
+    sd = synthetic.state_dict_like({k: tuple(v.shape) for k, v in model.state_dict().items()}, seed=seed)
+    model.load_state_dict(sd)
+    model = model.cuda().train().set_precision(precision)
+    return model, sd
+
+
+def rel(a: torch.Tensor, b: torch.Tensor) -> float:
+    a, b = a.detach().double().flatten().cpu(), b.detach().double().flatten().cpu()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def run_pair(version: str, size: int, batch: int, precision: str, loss: str = "focal", dc_rate=None,
+             oracle_device: str = "cpu", oracle_bf16: bool = False, oracle_dtype: torch.dtype = torch.float32):
+    """Returns dict with logits/loss/grads of both implementations (oracle tensors on CPU)."""
+    model, sd = build_model(version, precision, dc_rate)
+    x, y = synthetic.tiles(batch, size), synthetic.labels(batch, size)
+    masks = synthetic.drop_connect_masks(len(model.encoder.specs), batch, dc_rate)
+    if masks is not None:
+        binary, keep = masks
+        model.set_drop_connect_masks((binary / keep[:, None]).cuda())
+    a = alpha_weights()
+    # ---- oracle
+    dev = torch.device(oracle_device)
+    if dev.type == "cuda":
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+    sd_o = {k: (v.to(dev, oracle_dtype) if v.is_floating_point() else v.to(dev)) for k, v in sd.items()}
+    o_logits, o_loss, o_grads = O.loss_and_grads(sd_o, x.to(dev, oracle_dtype), y.to(dev), version, loss=loss,
+                                                 alpha=a.to(dev, oracle_dtype), gamma=2.0,
+                                                 ignore_index=0, skip_rule="generalised",
+                                                 dc_masks=None if masks is None else (masks[0].to(dev, oracle_dtype), masks[1].to(dev, oracle_dtype)),
+                                                 autocast_bf16=oracle_bf16)
+    # ---- CUDA path
+    fn = FocalLoss(a, 2.0, 0.0, ignore_index=0) if loss == "focal" else CrossEntropyLoss(a, ignore_index=0)
+    model.zero_grad(set_to_none=True)
+    logits = model(x.cuda())
+    val = fn(logits, y.cuda())
+    val.backward()
+    torch.cuda.synchronize()
+    grads = {k: p.grad for k, p in model.named_parameters() if p.grad is not None}
+    return dict(model=model, sd=sd, logits=logits.detach().float().cpu(), loss=float(val), grads=grads,
+                o_logits=o_logits.float().cpu(), o_loss=float(o_loss), o_grads={k: v.float().cpu() for k, v in o_grads.items()},
+                y=y)
+
+
+def grad_report(res, floor: float = 1e-6):
+    """[(rel_err, key, ours_norm, oracle_norm)] sorted worst first; theoretically-zero grads (oracle norm below
+    `floor` * max norm) are compared in absolute terms against that floor instead."""
+    rows = []
+    mx = max(float(v.norm()) for v in res["o_grads"].values())
+    for k, og in res["o_grads"].items():
+        g = res["grads"].get(k)
+        if g is None:
+            rows.append((float("inf"), k, 0.0, float(og.norm())))
+            continue
+        g = g.detach().float().cpu()
+        denom = max(float(og.double().norm()), floor * mx)
+        rows.append((float((g.double() - og.double()).norm()) / denom, k, float(g.norm()), float(og.norm())))
+    rows.sort(reverse=True)
+    return rows

@@ -13,6 +13,10 @@ import s2lc_b200  # noqa: E402,F401  (registers the package alias)
 
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 
+# torch references on the GPU must be true fp32 (cuDNN / cuBLAS default to TF32 for convs)
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a real B200 (run by the driver with -m gpu)")

@@ -1,0 +1,435 @@
+"""Per-kernel numerics on a real B200: every libs2lc kernel family (called through the C ABI) against the
+plain-PyTorch fp32 op it replaces, on seeded inputs.  Tolerances: fp32 storage 2e-5 relative (L2), bf16
+storage 1.5e-2 (the output rounding alone is 2^-9 per element)."""
+import ctypes as C
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+DT = {"fp32": (torch.float32, 0, 2e-5), "bf16": (torch.bfloat16, 1, 1.5e-2)}
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from s2lc_b200 import _lib
+    lib = _lib.load()
+    _lib.check(lib.s2lc_arch_check(0))
+    return lib
+
+
+def L():
+    from s2lc_b200 import _lib
+    return _lib
+
+
+def nhwc(x, dtype):  # [N,C,H,W] -> [N*H*W, C] contiguous
+    return x.permute(0, 2, 3, 1).reshape(-1, x.shape[1]).to(dtype).contiguous()
+
+
+def nchw(rows, n, h, w):
+    return rows.float().view(n, h, w, -1).permute(0, 3, 1, 2)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def same_pad(x, k, s):
+    h, w = x.shape[-2:]
+    oh, ow = math.ceil(h / s), math.ceil(w / s)
+    ph, pw = max((oh - 1) * s + k - h, 0), max((ow - 1) * s + k - w, 0)
+    return F.pad(x, [pw // 2, pw - pw // 2, ph // 2, ph - ph // 2])
+
+
+def mk(shape, seed, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return torch.randn(shape, generator=g, device="cuda") * scale
+
+
+def lazy(t, ld, scale=None, shift=None, gate=None, act=0):
+    return L().Lazy(t.data_ptr(), ld, L().ptr(scale), L().ptr(shift), L().ptr(gate), act, 0)
+
+
+def lazygrad(dy, ld, z=None, p=None, q=None, t=None, rs=None):
+    return L().LazyGrad(dy.data_ptr(), ld, L().ptr(z), ld, L().ptr(p), L().ptr(q), L().ptr(t), L().ptr(rs))
+
+
+# ----------------------------------------------------------------------------------------------- dwconv
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("k,s,h,w,c", [(3, 1, 24, 40, 48), (5, 1, 16, 16, 72), (3, 2, 32, 32, 144), (5, 2, 28, 28, 64),
+                                       (5, 2, 7, 7, 24), (3, 2, 15, 17, 8)])
+def test_dwconv_fwd_bwd(lib, prec, k, s, h, w, c):
+    dtype, dt, tol = DT[prec]
+    n = 2
+    x = mk((n, c, h, w), 1)
+    wt = mk((c, 1, k, k), 2, 0.3)
+    sc, sh = 1 + 0.1 * mk((c,), 3), 0.1 * mk((c,), 4)
+    xr = nhwc(x, dtype)
+    xq = nchw(xr, n, h, w).requires_grad_(True)          # the stored (rounded) input
+    wq = wt.clone().requires_grad_(True)
+    a = F.silu(xq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1))
+    if dtype == torch.bfloat16:
+        a = a + (a.to(dtype).float() - a).detach()        # the kernel stages activations in bf16
+    ref = F.conv2d(same_pad(a, k, s), wq, stride=s, groups=c)
+    ho, wo = ref.shape[-2:]
+    out = torch.empty(n * ho * wo, c, dtype=dtype, device="cuda")
+    stats = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    lz = lazy(xr, c, sc, sh, act=1)
+    L().check(lib.s2lc_dwconv_fwd(C.byref(lz), wt.data_ptr(), out.data_ptr(), stats.data_ptr(), n, h, w, c, k, s, dt,
+                                  stream()))
+    got = nchw(out, n, ho, wo)
+    assert rel_err(got, ref) < tol
+    assert rel_err(stats[:c], got.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(stats[c:], (got.double() ** 2).sum((0, 2, 3))) < 1e-5
+    # backward: lazy gradient g = p*dy + q*z + t on the output side
+    dy = mk((n, c, ho, wo), 5)
+    p_, q_, t_ = 1 + 0.1 * mk((c,), 6), 0.05 * mk((c,), 7), 0.01 * mk((c,), 8)
+    dyr = nhwc(dy, dtype)
+    g_ref = (p_.view(1, -1, 1, 1) * nchw(dyr, n, ho, wo) + q_.view(1, -1, 1, 1) * got + t_.view(1, -1, 1, 1))
+    if dtype == torch.bfloat16:
+        g_stage = g_ref.to(dtype).float()                 # bwd-data kernel stages the gradient tile in bf16
+    else:
+        g_stage = g_ref
+    gx, = torch.autograd.grad(ref, xq, g_stage, retain_graph=True)   # includes act'(u)*scale
+    gw, = torch.autograd.grad(ref, wq, g_ref)
+    # kernel returns d/d(BN output) i.e. without the *scale factor
+    gx_bnout = gx / sc.view(1, -1, 1, 1)
+    lg = lazygrad(dyr, c, out, p_, q_, t_)
+    dx = torch.empty(n * h * w, c, dtype=dtype, device="cuda")
+    st2 = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    L().check(lib.s2lc_dwconv_bwd_data(C.byref(lg), wt.data_ptr(), C.byref(lz), None, 0, dx.data_ptr(), c,
+                                       st2.data_ptr(), n, h, w, c, k, s, dt, stream()))
+    gotx = nchw(dx, n, h, w)
+    assert rel_err(gotx, gx_bnout) < tol * 2
+    assert rel_err(st2[:c], gotx.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(st2[c:], (gotx.double() * nchw(xr, n, h, w).double()).sum((0, 2, 3))) < 1e-5
+    dw = torch.zeros(c, 1, k, k, device="cuda")
+    L().check(lib.s2lc_dwconv_bwd_weight(C.byref(lg), C.byref(lz), dw.data_ptr(), n, h, w, c, k, s, dt, stream()))
+    assert rel_err(dw, gw) < tol * 2
+
+
+# ----------------------------------------------------------------------------------------------- implicit GEMM
+def pack(lib, wt, dtype, dt, n1, n2, taps, c, s1, s2, st, sc, flip=False, cpad=None):
+    from s2lc_b200._engine import PackedWeight
+    pw = PackedWeight(wt, dtype, n1, n2, taps, c, s1, s2, st, sc, flip, cpad)
+    L().check(lib.s2lc_weight_pack(*pw.args, stream()))
+    return pw
+
+
+def run_conv(lib, dt, mode, a, n, h, w, c, pw, out, ld_out, nout=None, bias=None, prev=None, stats=None, kind=0,
+             res1=None, ld_res1=0):
+    p = L().ConvParams()
+    p.mode, p.dtype, p.N, p.H, p.W, p.C = mode, dt, n, h, w, c
+    p.Cpad, p.Kpad, p.Nout, p.Npad = pw.cpad, pw.kpad, (pw.n_out if nout is None else nout), pw.npad
+    if isinstance(a, L().LazyGrad):
+        p.a_is_grad, p.a_bwd = 1, C.pointer(a)
+    else:
+        p.a_fwd = C.pointer(a)
+    p.w_packed, p.bias, p.out, p.ld_out = pw.buf.data_ptr(), L().ptr(bias), out.data_ptr(), ld_out
+    p.res1, p.ld_res1 = L().ptr(res1), ld_res1
+    if prev is not None:
+        p.prev = C.pointer(prev)
+    p.stats, p.stats_kind = L().ptr(stats), kind
+    L().check(lib.s2lc_conv_fwd(C.byref(p), stream()))
+
+
+def run_wgrad(lib, dt, mode, a, g, n, h, w, cin, cout, dw, db=None):
+    p = L().WgradParams(mode, dt, n, h, w, cin, cout, 0, C.pointer(a), C.pointer(g), dw.data_ptr(), L().ptr(db))
+    L().check(lib.s2lc_conv_wgrad(C.byref(p), stream()))
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("cin,cout,h,w,gated", [(24, 144, 16, 24, False), (144, 40, 12, 12, True), (512, 2048, 7, 7, False),
+                                                (32, 4, 32, 32, False), (1056, 176, 8, 8, True)])
+def test_conv1x1(lib, prec, cin, cout, h, w, gated):
+    dtype, dt, tol = DT[prec]
+    n = 2
+    x = mk((n, cin, h, w), 11)
+    wt = mk((cout, cin, 1, 1), 12, 1 / math.sqrt(cin))
+    sc, sh = 1 + 0.1 * mk((cin,), 13), 0.1 * mk((cin,), 14)
+    gate = torch.sigmoid(mk((n, cin), 15)) if gated else None
+    xr = nhwc(x, dtype)
+    xq = nchw(xr, n, h, w).requires_grad_(True)
+    wq = (wt.to(dtype).float() if dtype == torch.bfloat16 else wt.clone()).requires_grad_(True)
+    a = F.silu(xq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1))
+    if gated:
+        a = a * gate.view(n, cin, 1, 1)
+    if dtype == torch.bfloat16:
+        a = a + (a.to(dtype).float() - a).detach()     # tensor-core operand is rounded to bf16
+    ref = F.conv2d(a, wq)
+    pw = pack(lib, wt, dtype, dt, 1, cout, 1, cin, 0, cin, 0, 1)
+    out = torch.empty(n * h * w, cout, dtype=dtype, device="cuda")
+    stats = torch.zeros(2 * cout, dtype=torch.float64, device="cuda")
+    lz = lazy(xr, cin, sc, sh, gate, act=1)
+    run_conv(lib, dt, 0, lz, n, h, w, cin, pw, out, cout, stats=stats, kind=1)
+    got = nchw(out, n, h, w)
+    assert rel_err(got, ref) < tol
+    assert rel_err(stats[:cout], got.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(stats[cout:], (got.double() ** 2).sum((0, 2, 3))) < 1e-5
+    # weight gradient and data gradient (plain dy)
+    dy = mk((n, cout, h, w), 16)
+    dyr = nhwc(dy, dtype)
+    dyq = nchw(dyr, n, h, w)
+    gw, ga = torch.autograd.grad(ref, [wq, a], dyq)
+    lg = lazygrad(dyr, cout)
+    dw = torch.zeros_like(wt)
+    run_wgrad(lib, dt, 0, lz, lg, n, h, w, cin, cout, dw)
+    assert rel_err(dw, gw) < tol * 2
+    pwd = pack(lib, wt, dtype, dt, 1, cin, 1, cout, 0, 1, 0, cin)
+    da = torch.empty(n * h * w, cin, dtype=dtype, device="cuda")
+    run_conv(lib, dt, 0, lg, n, h, w, cout, pwd, da, cin)
+    assert rel_err(nchw(da, n, h, w), ga) < tol * 2
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("cin,cbuf,cout,h,w", [(38, 40, 32, 32, 32), (88, 88, 64, 16, 16), (640, 640, 512, 7, 7),
+                                               (64, 64, 64, 14, 14)])
+def test_conv3x3(lib, prec, cin, cbuf, cout, h, w):
+    dtype, dt, tol = DT[prec]
+    n = 2
+    x = mk((n, cbuf, h, w), 21)
+    x[:, cin:] = 0
+    wt = mk((cout, cin, 3, 3), 22, 1 / math.sqrt(9 * cin))
+    bias = 0.1 * mk((cout,), 23)
+    xr = nhwc(x, dtype)
+    xq = nchw(xr, n, h, w)[:, :cin].clone().requires_grad_(True)
+    wq = (wt.to(dtype).float() if dtype == torch.bfloat16 else wt.clone()).requires_grad_(True)
+    ref = F.conv2d(xq, wq, bias, padding=1)
+    pw = pack(lib, wt, dtype, dt, 1, cout, 9, cin, 0, cin * 9, 1, 9, cpad=cbuf)
+    out = torch.empty(n * h * w, cout, dtype=dtype, device="cuda")
+    stats = torch.zeros(2 * cout, dtype=torch.float64, device="cuda")
+    lz = lazy(xr, cbuf)
+    run_conv(lib, dt, 1, lz, n, h, w, cbuf, pw, out, cout, bias=bias, stats=stats, kind=1)
+    got = nchw(out, n, h, w)
+    assert rel_err(got, ref) < tol
+    assert rel_err(stats[:cout], got.double().sum((0, 2, 3))) < 1e-5
+    dy = mk((n, cout, h, w), 24)
+    dyr = nhwc(dy, dtype)
+    dyq = nchw(dyr, n, h, w)
+    gw, gx = torch.autograd.grad(ref, [wq, xq], dyq)
+    lg = lazygrad(dyr, cout)
+    dw, db = torch.zeros_like(wt), torch.zeros(cout, device="cuda")
+    run_wgrad(lib, dt, 1, lz, lg, n, h, w, cin, cout, dw, db)
+    assert rel_err(dw, gw) < tol * 2
+    assert rel_err(db, dyq.sum((0, 2, 3))) < tol
+    pwd = pack(lib, wt, dtype, dt, 1, cin, 9, cout, 0, 9, 1, cin * 9, flip=True)
+    ncol = (cin + 7) // 8 * 8
+    dx = torch.zeros(n * h * w, ncol, dtype=dtype, device="cuda")
+    run_conv(lib, dt, 1, lg, n, h, w, cout, pwd, dx, ncol)
+    assert rel_err(nchw(dx, n, h, w)[:, :cin], gx) < tol * 2
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("cin,cout,h,w", [(64, 32, 16, 16), (2048, 512, 7, 7), (128, 64, 9, 12)])
+def test_convT(lib, prec, cin, cout, h, w):
+    dtype, dt, tol = DT[prec]
+    n = 2
+    x = mk((n, cin, h, w), 31)
+    wt = mk((cin, cout, 2, 2), 32, 1 / math.sqrt(cin))
+    bias = 0.1 * mk((cout,), 33)
+    sc, sh = 1 + 0.1 * mk((cin,), 34), 0.1 * mk((cin,), 35)
+    xr = nhwc(x, dtype)
+    xq = nchw(xr, n, h, w).requires_grad_(True)
+    wq = (wt.to(dtype).float() if dtype == torch.bfloat16 else wt.clone()).requires_grad_(True)
+    a = F.relu(xq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1))
+    if dtype == torch.bfloat16:
+        a = a + (a.to(dtype).float() - a).detach()
+    ref = F.conv_transpose2d(a, wq, bias, stride=2)
+    pw = pack(lib, wt, dtype, dt, 4, cout, 1, cin, 1, 4, 0, cout * 4)
+    ccat = cout + 8
+    cat = torch.zeros(n * 4 * h * w, ccat, dtype=dtype, device="cuda")
+    lz = lazy(xr, cin, sc, sh, act=2)
+    run_conv(lib, dt, 2, lz, n, h, w, cin, pw, cat, ccat, bias=bias)
+    got = nchw(cat, n, 2 * h, 2 * w)[:, :cout]
+    assert rel_err(got, ref) < tol
+    assert float(cat[:, cout:].abs().max()) == 0.0
+    dy = mk((n, cout, 2 * h, 2 * w), 36)
+    dcat = torch.zeros(n * 4 * h * w, ccat, dtype=dtype, device="cuda")
+    dcat[:, :cout] = nhwc(dy, dtype)
+    dyq = nchw(dcat, n, 2 * h, 2 * w)[:, :cout]
+    gw, ga = torch.autograd.grad(ref, [wq, a], dyq)
+    lg = lazygrad(dcat, ccat)
+    dw, db = torch.zeros_like(wt), torch.zeros(cout, device="cuda")
+    run_wgrad(lib, dt, 2, lz, lg, n, h, w, cin, cout, dw, db)
+    assert rel_err(dw, gw) < tol * 2
+    assert rel_err(db, dyq.sum((0, 2, 3))) < tol
+    pwd = pack(lib, wt, dtype, dt, 1, cin, 4, cout, 0, cout * 4, 1, 4)
+    dx = torch.empty(n * h * w, cin, dtype=dtype, device="cuda")
+    st = torch.zeros(2 * cin, dtype=torch.float64, device="cuda")
+    run_conv(lib, dt, 3, lg, n, h, w, cout, pwd, dx, cin, prev=lz, stats=st, kind=2)
+    u = nchw(xr, n, h, w) * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1)
+    want = ga * (u > 0)
+    gotx = nchw(dx, n, h, w)
+    assert rel_err(gotx, want) < tol * 2
+    assert rel_err(st[cin:], (gotx.double() * nchw(xr, n, h, w).double()).sum((0, 2, 3))) < 1e-5
+
+
+# ----------------------------------------------------------------------------------------------- stem
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("h,w,co", [(64, 64, 48), (30, 34, 32)])
+def test_stem(lib, prec, h, w, co):
+    dtype, dt, tol = DT[prec]
+    n, cin = 2, 6
+    x = mk((n, cin, h, w), 41).requires_grad_(False)
+    wt = mk((co, cin, 3, 3), 42, 0.2).requires_grad_(True)
+    ref = F.conv2d(same_pad(x, 3, 2), wt, stride=2)
+    ho, wo = ref.shape[-2:]
+    out = torch.empty(n * ho * wo, co, dtype=dtype, device="cuda")
+    stats = torch.zeros(2 * co, dtype=torch.float64, device="cuda")
+    L().check(lib.s2lc_stem_conv_fwd(x.data_ptr(), wt.data_ptr(), out.data_ptr(), stats.data_ptr(), n, cin, h, w, co,
+                                     dt, stream()))
+    got = nchw(out, n, ho, wo)
+    assert rel_err(got, ref) < (tol if prec == "fp32" else 4e-3)
+    assert rel_err(stats[co:], (got.double() ** 2).sum((0, 2, 3))) < 1e-5
+    dy = mk((n, co, ho, wo), 43)
+    dyr = nhwc(dy, dtype)
+    gw, = torch.autograd.grad(ref, wt, nchw(dyr, n, ho, wo))
+    dw = torch.zeros_like(wt)
+    lg = lazygrad(dyr, co)
+    L().check(lib.s2lc_stem_conv_wgrad(x.data_ptr(), C.byref(lg), dw.data_ptr(), n, cin, h, w, co, dt, stream()))
+    assert rel_err(dw, gw) < tol
+
+
+# ----------------------------------------------------------------------------------------------- BN / SE / misc
+def test_bn_finalize_and_backward_coefficients(lib):
+    c, n, h, w = 40, 3, 9, 11
+    z = mk((n, c, h, w), 51) * 2 + 0.5
+    gamma, beta = 1 + 0.1 * mk((c,), 52), 0.1 * mk((c,), 53)
+    rm, rv = 0.1 * mk((c,), 54), 1 + 0.1 * mk((c,), 55).abs()
+    rm0, rv0 = rm.clone(), rv.clone()
+    zz = z.clone().requires_grad_(True)
+    y = F.batch_norm(zz, rm0, rv0, gamma, beta, training=True, momentum=0.01, eps=1e-3)
+    stats = torch.cat([z.double().sum((0, 2, 3)), (z.double() ** 2).sum((0, 2, 3))]).contiguous()
+    outs = [torch.empty(c, device="cuda") for _ in range(4)]
+    cnt = float(n * h * w)
+    L().check(lib.s2lc_bn_finalize(stats.data_ptr(), gamma.data_ptr(), beta.data_ptr(), cnt, 1e-3, 0.01, rm.data_ptr(),
+                                   rv.data_ptr(), *[o.data_ptr() for o in outs], c, stream()))
+    scale, shift, mean, invstd = outs
+    assert rel_err(z * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1), y) < 1e-5
+    assert rel_err(rm, rm0) < 1e-6 and rel_err(rv, rv0) < 1e-6
+    dy = mk((n, c, h, w), 56)
+    gz, gg, gb = torch.autograd.grad(y, [zz, gamma.requires_grad_(True), beta.requires_grad_(True)], dy, allow_unused=True) \
+        if False else (None, None, None)
+    zz2 = z.clone().requires_grad_(True)
+    g2, b2 = gamma.detach().clone().requires_grad_(True), beta.detach().clone().requires_grad_(True)
+    y2 = F.batch_norm(zz2, None, None, g2, b2, training=True, eps=1e-3)
+    gz, gg, gb = torch.autograd.grad(y2, [zz2, g2, b2], dy)
+    st = torch.cat([dy.double().sum((0, 2, 3)), (dy.double() * z.double()).sum((0, 2, 3))]).contiguous()
+    p, q, t, dg, db = [torch.empty(c, device="cuda") for _ in range(5)]
+    L().check(lib.s2lc_bn_bwd_finalize(st.data_ptr(), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(), cnt,
+                                       p.data_ptr(), q.data_ptr(), t.data_ptr(), dg.data_ptr(), db.data_ptr(), c,
+                                       stream()))
+    got = p.view(1, -1, 1, 1) * dy + q.view(1, -1, 1, 1) * z + t.view(1, -1, 1, 1)
+    assert rel_err(got, gz) < 2e-5
+    assert rel_err(dg, gg) < 2e-5 and rel_err(db, gb) < 2e-5
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_squeeze_excite(lib, prec):
+    dtype, dt, tol = DT[prec]
+    n, c, s, h, w = 3, 48, 12, 10, 14
+    z = mk((n, c, h, w), 61)
+    sc, sh = 1 + 0.1 * mk((c,), 62), 0.1 * mk((c,), 63)
+    w1, b1, w2, b2 = mk((s, c), 64, 0.2), 0.1 * mk((s,), 65), mk((c, s), 66, 0.2), 0.1 * mk((c,), 67)
+    zr = nhwc(z, dtype)
+    zq = nchw(zr, n, h, w).requires_grad_(True)
+    ps = [t.clone().requires_grad_(True) for t in (w1, b1, w2, b2)]
+    a = F.silu(zq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1))
+    pooled_ref = a.mean((2, 3))
+    gate_ref = torch.sigmoid(F.linear(F.silu(F.linear(pooled_ref, ps[0], ps[1])), ps[2], ps[3]))
+    out_ref = a * gate_ref.view(n, c, 1, 1)
+    pooled, gate = torch.empty(n, c, device="cuda"), torch.empty(n, c, device="cuda")
+    lz = lazy(zr, c, sc, sh, act=1)
+    L().check(lib.s2lc_se_pool(C.byref(lz), pooled.data_ptr(), n, h * w, c, dt, stream()))
+    L().check(lib.s2lc_se_fc_fwd(pooled.data_ptr(), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(),
+                                 gate.data_ptr(), n, c, s, stream()))
+    assert rel_err(pooled, pooled_ref) < 1e-5 and rel_err(gate, gate_ref) < 1e-5
+    da_t = mk((n, c, h, w), 68)
+    dar = nhwc(da_t, dtype)
+    daq = nchw(dar, n, h, w)
+    grads = torch.autograd.grad(out_ref, [zq, *ps], daq)
+    dgate, dpool = torch.empty(n, c, device="cuda"), torch.empty(n, c, device="cuda")
+    dws = [torch.empty_like(t) for t in (w1, b1, w2, b2)]
+    scratch = torch.empty(n * (c + 2 * s), device="cuda")
+    L().check(lib.s2lc_se_bwd_reduce(dar.data_ptr(), c, C.byref(lz), dgate.data_ptr(), n, h * w, c, dt, stream()))
+    L().check(lib.s2lc_se_fc_bwd(pooled.data_ptr(), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(),
+                                 dgate.data_ptr(), dpool.data_ptr(), *[d.data_ptr() for d in dws], scratch.data_ptr(),
+                                 n, c, s, stream()))
+    lzg = lazy(zr, c, sc, sh, gate, act=1)
+    st = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    L().check(lib.s2lc_se_bwd_apply(dar.data_ptr(), c, C.byref(lzg), dpool.data_ptr(), st.data_ptr(), n, h * w, c, dt,
+                                    stream()))
+    got = nchw(dar, n, h, w)                       # d/d(BN2 output)
+    want = grads[0] / sc.view(1, -1, 1, 1)
+    assert rel_err(got, want) < tol
+    for d, g in zip(dws, grads[1:]):
+        assert rel_err(d, g) < 1e-4
+    assert rel_err(st[:c], got.double().sum((0, 2, 3))) < 1e-5
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_bn_apply_and_reduce(lib, prec):
+    dtype, dt, tol = DT[prec]
+    n, c, h, w = 2, 24, 12, 12
+    z, res = mk((n, c, h, w), 71), mk((n, c, h, w), 72)
+    sc, sh = 1 + 0.1 * mk((c,), 73), 0.1 * mk((c,), 74)
+    rs = torch.tensor([0.0, 1.25], device="cuda")
+    zr, rr = nhwc(z, dtype), nhwc(res, dtype)
+    out = torch.empty_like(zr)
+    lz = lazy(zr, c, sc, sh)
+    L().check(lib.s2lc_bn_apply(C.byref(lz), rr.data_ptr(), c, rs.data_ptr(), out.data_ptr(), c, n * h * w, c, h * w, dt,
+                                stream()))
+    want = (nchw(zr, n, h, w) * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1)) * rs.view(n, 1, 1, 1) + nchw(rr, n, h, w)
+    assert rel_err(nchw(out, n, h, w), want) < tol
+    st = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    L().check(lib.s2lc_bn_bwd_reduce(rr.data_ptr(), c, zr.data_ptr(), c, rs.data_ptr(), st.data_ptr(), n * h * w, c,
+                                     h * w, dt, stream()))
+    d = nchw(rr, n, h, w).double() * rs.view(n, 1, 1, 1)
+    assert rel_err(st[:c], d.sum((0, 2, 3))) < 1e-6
+    assert rel_err(st[c:], (d * nchw(zr, n, h, w).double()).sum((0, 2, 3))) < 1e-6
+
+
+def test_loss_against_golden(golden_arrays):
+    from s2lc_b200.losses import CrossEntropyLoss, FocalLoss
+    from s2lc_b200 import synthetic
+    alpha = torch.tensor(synthetic.CLASS_DISTRIBUTION)
+    alpha[1:] = 1 - alpha[1:]
+    y = torch.from_numpy(golden_arrays["loss/y"]).cuda()
+    cases = {"focal_g2": FocalLoss(alpha, 2.0, 0.0, ignore_index=0),
+             "focal_g0.5_noignore": FocalLoss(torch.ones(4), 0.5, 0.0),
+             "focal_g2_sum": FocalLoss(alpha, 2.0, 0.0, ignore_index=0, reduce_type="sum"),
+             "ce_weighted": CrossEntropyLoss(alpha, ignore_index=0), "ce_plain": CrossEntropyLoss()}
+    for nm, fn in cases.items():
+        lg = torch.from_numpy(golden_arrays["loss/logits"]).cuda().requires_grad_(True)
+        v = fn(lg, y)
+        v.backward()
+        want_v = float(golden_arrays[f"loss/{nm}/value"])
+        assert abs(float(v) - want_v) <= 2e-5 * max(1.0, abs(want_v)), nm
+        assert rel_err(lg.grad.cpu(), torch.from_numpy(golden_arrays[f"loss/{nm}/dlogits"])) < 1e-4, nm
+
+
+def test_loss_label_smoothing_matches_torch():
+    from s2lc_b200.losses import CrossEntropyLoss, FocalLoss
+    lg = (2 * mk((2, 4, 16, 16), 81))
+    y = torch.randint(0, 4, (2, 16, 16), device="cuda", generator=torch.Generator(device="cuda").manual_seed(82))
+    wts = torch.tensor([0.2, 0.5, 0.9, 0.7], device="cuda")
+    a = lg.clone().requires_grad_(True)
+    b = lg.clone().requires_grad_(True)
+    v = CrossEntropyLoss(wts, label_smoothing=0.1, ignore_index=1)(a, y)
+    r = F.cross_entropy(b, y, weight=wts, label_smoothing=0.1, ignore_index=1)
+    v.backward()
+    r.backward()
+    assert abs(float(v) - float(r)) < 1e-5 and rel_err(a.grad, b.grad) < 1e-4
+    a.grad = b.grad = None
+    v = FocalLoss(wts, 1.5, 0.05, ignore_index=1)(a, y)
+    ce = F.cross_entropy(b, y, label_smoothing=0.05, ignore_index=1, reduction="none")
+    r = (wts[y] * (1 - torch.exp(-ce)) ** 1.5 * ce).mean()
+    v.backward()
+    r.backward()
+    assert abs(float(v) - float(r)) < 1e-5 and rel_err(a.grad, b.grad) < 1e-4
