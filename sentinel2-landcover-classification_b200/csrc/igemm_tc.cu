@@ -398,6 +398,4 @@ int32_t launch_conv_tc(const ConvArgs& A, cudaStream_t st) {
   return check_launch("conv_tc");
 }
 
-int32_t launch_wgrad_tc(const WgradArgs&, cudaStream_t) { return 1; }   // wgrad_tc.cu takes over when it lands
-
 }  // namespace s2lc

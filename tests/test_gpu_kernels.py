@@ -270,6 +270,53 @@ def test_convT(lib, prec, cin, cout, h, w):
     assert rel_err(st[cin:], (gotx.double() * nchw(xr, n, h, w).double()).sum((0, 2, 3))) < 1e-5
 
 
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("mode,cin,cout,n,h,w", [(0, 40, 240, 3, 20, 20), (0, 304, 1824, 2, 9, 9), (0, 1824, 304, 2, 9, 9),
+                                                 (1, 88, 64, 3, 20, 12), (1, 320, 256, 1, 16, 16), (1, 40, 32, 2, 50, 30),
+                                                 (2, 64, 32, 3, 10, 14), (2, 512, 256, 1, 8, 8)])
+def test_wgrad_lazy_operands(lib, prec, mode, cin, cout, n, h, w):
+    """Weight gradients with BOTH operands lazy (BatchNorm-backward affine + drop-connect row scale on G;
+    BatchNorm + SiLU + squeeze-excite gate on A), ragged pixel counts (partial 64-pixel blocks, several slabs)
+    and channel counts that need several tensor-core tiles — the tcgen05 wgrad engine's whole feature set."""
+    dtype, dt, tol = DT[prec]
+    up = 2 if mode == 2 else 1
+    x = mk((n, cin, h, w), 51)
+    sc, sh = 1 + 0.1 * mk((cin,), 52), 0.1 * mk((cin,), 53)
+    gate = torch.sigmoid(mk((n, cin), 54)) if mode == 0 else None
+    xr = nhwc(x, dtype)
+    a = F.silu(nchw(xr, n, h, w) * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1))
+    if gate is not None:
+        a = a * gate.view(n, cin, 1, 1)
+    dy, z = mk((n, cout, up * h, up * w), 55), mk((n, cout, up * h, up * w), 56)
+    dyr, zr = nhwc(dy, dtype), nhwc(z, dtype)
+    use_bn = mode != 2                      # the transposed conv feeds the concat buffer: no BatchNorm behind it
+    p_, q_, t_ = 1 + 0.1 * mk((cout,), 57), 0.05 * mk((cout,), 58), 0.01 * mk((cout,), 59)
+    rs = 0.5 + torch.rand(n, device="cuda")
+    g = nchw(dyr, n, up * h, up * w) * rs.view(n, 1, 1, 1)
+    if use_bn:
+        g = p_.view(1, -1, 1, 1) * g + q_.view(1, -1, 1, 1) * nchw(zr, n, up * h, up * w) + t_.view(1, -1, 1, 1)
+    if dtype == torch.bfloat16:             # tensor-core operands are rounded to bf16
+        a, g = a.to(dtype).float(), g.to(dtype).float()
+    if mode == 0:
+        want = torch.einsum("nohw,nihw->oi", g, a).view(cout, cin, 1, 1)
+    elif mode == 1:
+        ap = F.pad(a, [1, 1, 1, 1])
+        want = torch.stack([torch.einsum("nohw,nihw->oi", g, ap[:, :, ky:ky + h, kx:kx + w])
+                            for ky in range(3) for kx in range(3)], -1).view(cout, cin, 3, 3)
+    else:
+        want = torch.stack([torch.einsum("nihw,nohw->io", a, g[:, :, qy::2, qx::2])
+                            for qy in range(2) for qx in range(2)], -1).view(cin, cout, 2, 2)
+    lz = lazy(xr, cin, sc, sh, gate, act=1)
+    lg = lazygrad(dyr, cout, zr if use_bn else None, p_ if use_bn else None, q_ if use_bn else None,
+                  t_ if use_bn else None, rs)
+    dw = torch.zeros_like(want)
+    db = torch.zeros(cout, device="cuda") if mode != 0 else None
+    run_wgrad(lib, dt, mode, lz, lg, n, h, w, cin, cout, dw, db)
+    assert rel_err(dw, want) < (5e-5 if prec == "fp32" else 2e-3)   # bf16: fp32 accumulation of identical operands
+    if db is not None:
+        assert rel_err(db, g.sum((0, 2, 3))) < (5e-5 if prec == "fp32" else 2e-3)
+
+
 # ----------------------------------------------------------------------------------------------- stem
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("h,w,co", [(64, 64, 48), (30, 34, 32)])
