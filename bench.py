@@ -250,7 +250,7 @@ def kernel_breakdown(trainer, model, ws, x, y, pk, pk_kind) -> dict:
     torch.cuda.synchronize()
     agg: dict[str, list] = {}
     for metas, evs in ((ws.fwd_meta, ev_f), (ws.bwd_meta, ev_b)):
-        for (label, nbytes, flops), (e0, e1) in zip(metas, evs):
+        for (label, nbytes, flops, _desc), (e0, e1) in zip(metas, evs):
             r = agg.setdefault(label, [0, 0.0, 0.0, 0.0])
             r[0] += 1
             r[1] += e0.elapsed_time(e1)

@@ -194,11 +194,11 @@ class Workspace:
 
     def F(self, name: str, *args, nbytes: float = 0, flops: float = 0) -> None:
         self.fwd_list.append((getattr(self.lib, name), args))
-        self.fwd_meta.append([name[5:], nbytes, flops])
+        self.fwd_meta.append([name[5:], nbytes, flops, ""])
 
     def B(self, name: str, *args, nbytes: float = 0, flops: float = 0) -> None:
         self.bwd_list.append((getattr(self.lib, name), args))
-        self.bwd_meta.append([name[5:], nbytes, flops])
+        self.bwd_meta.append([name[5:], nbytes, flops, ""])
 
     def conv(self, lst, mode: int, a, n: int, h: int, w: int, c: int, pw: PackedWeight, out, ld_out: int, *, nout=None,
              bias=None, res1=None, ld_res1: int = 0, res2=None, ld_res2: int = 0, prev=None, stats=None,
@@ -239,7 +239,8 @@ class Workspace:
         label = {L.CONV_1X1: "conv1x1", L.CONV_3X3: "conv3x3", L.CONVT_FWD: "convT", L.CONVT_DGRAD: "convT_dgrad"}[mode]
         if lst is self.bwd_list and mode != L.CONVT_DGRAD:
             label += "_dgrad"
-        (self.fwd_meta if lst is self.fwd_list else self.bwd_meta).append([label, nbytes, 2.0 * rows * taps * c * p.Nout])
+        (self.fwd_meta if lst is self.fwd_list else self.bwd_meta).append(
+            [label, nbytes, 2.0 * rows * taps * c * p.Nout, f"{n}x{h}x{w} {c}->{p.Nout}"])
 
     def wgrad(self, mode: int, a: L.Lazy, g: L.LazyGrad, n: int, h: int, w: int, cin: int, cout: int, dw: int,
               dbias: int | None = None) -> None:
@@ -251,14 +252,14 @@ class Workspace:
         grp = 4 if mode == L.CONVT_FWD else 1
         nbytes = rows * cin * es + rows * grp * cout * es * (2 if g.z else 1) + 4 * taps * grp * cin * cout
         label = {L.CONV_1X1: "conv1x1_wgrad", L.CONV_3X3: "conv3x3_wgrad", L.CONVT_FWD: "convT_wgrad"}[mode]
-        self.bwd_meta.append([label, nbytes, 2.0 * rows * taps * grp * cin * cout])
+        self.bwd_meta.append([label, nbytes, 2.0 * rows * taps * grp * cin * cout, f"{n}x{h}x{w} {cin}->{cout}"])
 
     def gptr(self, key: str) -> int:
         self._grad_write_idx[key] = len(self.bwd_list)   # the launch appended next writes this gradient
         return self.eng.grad_views[key].data_ptr()
 
-    def meta(self, lst_meta: list, nbytes: float, flops: float = 0.0) -> None:
-        lst_meta[-1][1], lst_meta[-1][2] = nbytes, flops
+    def meta(self, lst_meta: list, nbytes: float, flops: float = 0.0, desc: str = "") -> None:
+        lst_meta[-1][1], lst_meta[-1][2], lst_meta[-1][3] = nbytes, flops, desc
 
     # ---------------------------------------------------------------- BatchNorm helpers
     def bn_forward(self, bn: _BN) -> None:
@@ -324,7 +325,7 @@ class Workspace:
         self.dc_step = C.c_uint64(0)
         if use_dc:
             self.fwd_list.append(("DC", ()))   # resolved in run_forward (internal generator or injected masks)
-            self.fwd_meta.append(["dropconnect_masks", 0, 0])
+            self.fwd_meta.append(["dropconnect_masks", 0, 0, ""])
 
         def dc_ptr(i: int):
             if self.dc is None or not specs[i].residual:
@@ -353,6 +354,7 @@ class Workspace:
             bm = enc.blocks[i]
             rec = type("Rec", (), {})()
             rec.sp, rec.h_in, rec.w_in = sp, cur_h, cur_w
+            bd = f"blk{i} {N}x{cur_h}x{cur_w} C{sp.c_exp} k{sp.kernel}s{sp.stride}"
             rows_in = N * cur_h * cur_w
             ho, wo = (cur_h + sp.stride - 1) // sp.stride, (cur_w + sp.stride - 1) // sp.stride
             rows_out = N * ho * wo
@@ -378,7 +380,7 @@ class Workspace:
             rec.bn2 = _BN(self, bn2m, rows_out)
             self.F("s2lc_dwconv_fwd", C.byref(rec.dw_in), dwc.weight.data_ptr(), rec.z2.data_ptr(),
                    self.stats_f(rec.bn2), N, cur_h, cur_w, sp.c_exp, sp.kernel, sp.stride, self.dt)
-            self.meta(self.fwd_meta, (rows_in + rows_out) * sp.c_exp * self.es, 2.0 * rows_out * sp.c_exp * sp.kernel ** 2)
+            self.meta(self.fwd_meta, (rows_in + rows_out) * sp.c_exp * self.es, 2.0 * rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
             self.bn_forward(rec.bn2)
             se1, se2 = bm.squeeze_excitation[1], bm.squeeze_excitation[3]
             rec.se1, rec.se2 = se1, se2
@@ -386,7 +388,7 @@ class Workspace:
             rec.s2_nogate = self.lazy(rec.z2, sp.c_exp, rec.bn2.scale, rec.bn2.shift, act=L.ACT_SILU)
             rec.s2_gated = self.lazy(rec.z2, sp.c_exp, rec.bn2.scale, rec.bn2.shift, gate=rec.gate, act=L.ACT_SILU)
             self.F("s2lc_se_pool", C.byref(rec.s2_nogate), rec.pooled.data_ptr(), N, ho * wo, sp.c_exp, self.dt)
-            self.meta(self.fwd_meta, rows_out * sp.c_exp * self.es)
+            self.meta(self.fwd_meta, rows_out * sp.c_exp * self.es, desc=bd)
             self.F("s2lc_se_fc_fwd", rec.pooled.data_ptr(), se1.weight.data_ptr(), se1.bias.data_ptr(),
                    se2.weight.data_ptr(), se2.bias.data_ptr(), rec.gate.data_ptr(), N, sp.c_exp, sp.c_se)
             conv3, bn3m = bm.final_layer[0], bm.final_layer[1]
@@ -401,7 +403,7 @@ class Workspace:
             rec.z3_lazy = self.lazy(rec.z3, sp.c_out, rec.bn3.scale, rec.bn3.shift)
             self.F("s2lc_bn_apply", C.byref(rec.z3_lazy), Y_prev.data_ptr() if sp.residual else None, sp.c_out,
                    dc_ptr(i), rec.Y.data_ptr(), sp.c_out, rows_out, sp.c_out, ho * wo, self.dt)
-            self.meta(self.fwd_meta, rows_out * sp.c_out * self.es * (3 if sp.residual else 2))
+            self.meta(self.fwd_meta, rows_out * sp.c_out * self.es * (3 if sp.residual else 2), desc=bd)
             rec.is_skip = (ho, wo) not in seen_hw and (ho, wo) != head_hw
             if rec.is_skip:
                 seen_hw.add((ho, wo))
@@ -572,6 +574,7 @@ class Workspace:
             sp = rec.sp
             dYi = dY[i % 2]
             ho, wo, hi, wi = rec.h_out, rec.w_out, rec.h_in, rec.w_in
+            bd = f"blk{i} {N}x{hi}x{wi} C{sp.c_exp} k{sp.kernel}s{sp.stride}"
             self.bn_backward(rec.bn3, rec.kbn3)
             g3 = self.lazygrad(dYi, sp.c_out, rec.z3, sp.c_out, rec.bn3, rowscale=dc_ptr(i))
             self.wgrad(L.CONV_1X1, rec.s2_gated, g3, N, ho, wo, sp.c_exp, sp.c_out, self.gptr(rec.k3 + ".weight"))
@@ -581,20 +584,20 @@ class Workspace:
             kse = f"encoder.blocks.{i}.squeeze_excitation"
             self.B("s2lc_se_bwd_reduce", da_buf.data_ptr(), sp.c_exp, C.byref(rec.s2_nogate), dgate.data_ptr(), N,
                    ho * wo, sp.c_exp, self.dt)
-            self.meta(self.bwd_meta, 2 * rec.rows_out * sp.c_exp * self.es)
+            self.meta(self.bwd_meta, 2 * rec.rows_out * sp.c_exp * self.es, desc=bd)
             self.B("s2lc_se_fc_bwd", rec.pooled.data_ptr(), rec.se1.weight.data_ptr(), rec.se1.bias.data_ptr(),
                    rec.se2.weight.data_ptr(), rec.se2.bias.data_ptr(), dgate.data_ptr(), dpool.data_ptr(),
                    self.gptr(kse + ".1.weight"), self.gptr(kse + ".1.bias"), self.gptr(kse + ".3.weight"),
                    self.gptr(kse + ".3.bias"), se_scratch.data_ptr(), N, sp.c_exp, sp.c_se)
             self.B("s2lc_se_bwd_apply", da_buf.data_ptr(), sp.c_exp, C.byref(rec.s2_gated), dpool.data_ptr(),
                    ("SB", rec.bn2.st_b), N, ho * wo, sp.c_exp, self.dt)
-            self.meta(self.bwd_meta, 3 * rec.rows_out * sp.c_exp * self.es)
+            self.meta(self.bwd_meta, 3 * rec.rows_out * sp.c_exp * self.es, desc=bd)
             self.bn_backward(rec.bn2, rec.kbn2)
             g2 = self.lazygrad(da_buf, sp.c_exp, rec.z2, sp.c_exp, rec.bn2)
             self.B("s2lc_dwconv_bwd_weight", C.byref(g2), C.byref(rec.dw_in), self.gptr(rec.kdw + ".weight"), N, hi, wi,
                    sp.c_exp, sp.kernel, sp.stride, self.dt)
             self.meta(self.bwd_meta, (2 * rec.rows_out + rec.rows_in) * sp.c_exp * self.es,
-                      2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
+                      2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
             prev_rec = blocks[i - 1] if i > 0 else None
             if prev_rec is not None:
                 psk_ptr, psk_ld = skip_grad(prev_rec)
@@ -603,7 +606,7 @@ class Workspace:
                        dy1_buf.data_ptr(), sp.c_exp, ("SB", rec.bn1.st_b), N, hi, wi, sp.c_exp, sp.kernel, sp.stride,
                        self.dt)
                 self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
-                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
+                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
                 self.bn_backward(rec.bn1, rec.kbn1)
                 g1 = self.lazygrad(dy1_buf, sp.c_exp, rec.z1, sp.c_exp, rec.bn1)
                 self.wgrad(L.CONV_1X1, rec.x_lazy, g1, N, hi, wi, sp.c_in, sp.c_exp, self.gptr(rec.k1 + ".weight"))
@@ -621,20 +624,20 @@ class Workspace:
                        dYi.data_ptr() if sp.residual else None, sp.c_out, dYp.data_ptr(), sp.c_in, None, N, hi, wi,
                        sp.c_exp, sp.kernel, sp.stride, self.dt)
                 self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
-                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
+                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
                 if psk_ptr is not None:
                     self.B("s2lc_add_slice", dYp.data_ptr(), sp.c_in, psk_ptr, psk_ld, dYp.data_ptr(), sp.c_in,
                            rec.rows_in, sp.c_in, self.dt)
                 self.B("s2lc_bn_bwd_reduce", dYp.data_ptr(), sp.c_in, prev_rec.z3.data_ptr(), sp.c_in, dc_ptr(i - 1),
                        ("SB", prev_rec.bn3.st_b), rec.rows_in, sp.c_in, hi * wi, self.dt)
-                self.meta(self.bwd_meta, 2 * rec.rows_in * sp.c_in * self.es)
+                self.meta(self.bwd_meta, 2 * rec.rows_in * sp.c_in * self.es, desc=bd)
             else:
                 # block 0: input is the lazy stem output -> gradient w.r.t. the stem BatchNorm output
                 dy0 = dy1_buf
                 self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), None, 0,
                        dy0.data_ptr(), c0, ("SB", bn0.st_b), N, hi, wi, sp.c_exp, sp.kernel, sp.stride, self.dt)
                 self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
-                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2)
+                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
                 self.bn_backward(bn0, "encoder.stem.1")
                 g0 = self.lazygrad(dy0, c0, z0, c0, bn0)
                 self.B("s2lc_stem_conv_wgrad", self.x_ptr, C.byref(g0), self.gptr("encoder.stem.0.weight"), N,

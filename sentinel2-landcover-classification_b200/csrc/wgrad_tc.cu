@@ -12,7 +12,7 @@
 // Layout in smem: SWIZZLE_128B MN-major atoms of 8 pixels x 64 channels (1 KB); a 64-pixel pipeline block of a
 // 64-channel group is 8 KB (SBO = 1 KB between 8-pixel groups), channel groups are LBO = 8 KB apart.
 //
-// Warp specialisation: 8 loader warps (gather + transform + st.shared, arrive on `full` mbarriers), 1 MMA warp
+// Warp specialisation: 16 loader warps (gather + transform + st.shared, arrive on `full` mbarriers), 1 MMA warp
 // (one elected lane issues tcgen05.mma, tcgen05.commit releases the slots), accumulators live in TMEM for the
 // whole pixel slab; the loader warps become the epilogue (tcgen05.ld -> fp32 atomicAdd into the reference-layout
 // gradient).  For the 3x3 convs ONE CTA accumulates all nine taps (9 accumulators of [128 x 48] fp32 = 432 TMEM
@@ -26,12 +26,11 @@ namespace s2lc {
 using namespace tc;
 
 constexpr int WG_BK = 64;                 // pixels per pipeline block (GEMM K per stage)
-constexpr int WG_LOAD_WARPS = 8;
+constexpr int WG_LOAD_WARPS = 16;
 constexpr int WG_LOAD_THREADS = WG_LOAD_WARPS * 32;
 constexpr int WG_THREADS = WG_LOAD_THREADS + 32;
 constexpr int WG_GROUP_BYTES = 8192;      // 64 pixels x 64 channels bf16
-constexpr int WG_MAXP = 8;                // max loader passes per tile (256-wide N tile: 32 chunks/pixel)
-constexpr int WG_MAX_SG = 6, WG_MAX_SA = 20;
+constexpr int WG_MAX_STAGES = 8;
 
 struct WgPlan {
   int g_on_m;       // 1: G channels on the M (TMEM lane) side and A on the N side; 0: swapped
@@ -39,8 +38,8 @@ struct WgPlan {
   int ntpad;        // MMA N (multiple of 16)
   int n_ntiles;     // tiles along the N side
   int taps;         // 9 (3x3) or 1
-  int SG, SA;       // ring depths
-  int gsz, asz;     // slot bytes
+  int stages;       // ring depth; one stage = the G tile + `taps` A tiles of one 64-pixel block
+  int gsz, asz;     // tile bytes
   int tmem_cols;
   int slabs;
   int64_t px_per_slab;   // multiple of WG_BK
@@ -75,17 +74,18 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 }
 __device__ __forceinline__ void loaders_sync() { asm volatile("bar.sync 1, %0;" ::"n"(WG_LOAD_THREADS) : "memory"); }
 
+// TAPS: 9 (3x3, all taps accumulated by one CTA) or 1.  MAXPG / MAXPA: compile-time bound on the number of loader
+// passes over the G / A tile (a pass = 512 threads x one 16 B chunk); every global load of a pixel block is issued
+// before the first transform so that ~13 independent 16 B loads per thread are in flight (HBM latency hiding).
+template <int TAPS, int MAXPG, int MAXPA>
 __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, WgPlan K) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  unsigned char* ringG = smem;
-  unsigned char* ringA = smem + K.SG * K.gsz;
-  uint64_t* fullG = reinterpret_cast<uint64_t*>(ringA + K.SA * K.asz);
-  uint64_t* emptyG = fullG + WG_MAX_SG;
-  uint64_t* fullA = emptyG + WG_MAX_SG;
-  uint64_t* emptyA = fullA + WG_MAX_SA;
-  uint64_t* done = emptyA + WG_MAX_SA;
+  const int stage_bytes = K.gsz + TAPS * K.asz;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + K.stages * stage_bytes);
+  uint64_t* empty = full + WG_MAX_STAGES;
+  uint64_t* done = empty + WG_MAX_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
   float* sbias = reinterpret_cast<float*>(tmem_slot + 2);   // [256]
 
@@ -105,8 +105,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
   const int a_cw = (Ca - a_c0) < a_tw ? (Ca - a_c0) : a_tw;
 
   if (tid == 0) {
-    for (int s = 0; s < K.SG; ++s) { mbar_init(&fullG[s], WG_LOAD_WARPS); mbar_init(&emptyG[s], 1); }
-    for (int s = 0; s < K.SA; ++s) { mbar_init(&fullA[s], WG_LOAD_WARPS); mbar_init(&emptyA[s], 1); }
+    for (int s = 0; s < K.stages; ++s) { mbar_init(&full[s], WG_LOAD_WARPS); mbar_init(&empty[s], 1); }
     mbar_init(done, 1);
     fence_barrier_init();
   }
@@ -122,14 +121,13 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
     if (lane == 0 && nblk > 0) {
       const uint32_t idesc = idesc_bf16(128, (uint32_t)K.ntpad, 1, 1);   // both operands MN-major
       for (int blk = 0; blk < nblk; ++blk) {
-        const int sg = blk % K.SG;
-        mbar_wait(&fullG[sg], (uint32_t)((blk / K.SG) & 1));
-        const uint32_t g_addr = smem_u32(ringG + sg * K.gsz);
-        for (int t = 0; t < K.taps; ++t) {
-          const int ia = blk * K.taps + t, sa = ia % K.SA;
-          mbar_wait(&fullA[sa], (uint32_t)((ia / K.SA) & 1));
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(ringA + sa * K.asz);
+        const int s = blk % K.stages;
+        mbar_wait(&full[s], (uint32_t)((blk / K.stages) & 1));
+        tc_fence_after();
+        const uint32_t g_addr = smem_u32(smem + s * stage_bytes);
+#pragma unroll
+        for (int t = 0; t < TAPS; ++t) {
+          const uint32_t a_addr = g_addr + K.gsz + t * K.asz;
           const uint32_t m_addr = K.g_on_m ? g_addr : a_addr, n_addr = K.g_on_m ? a_addr : g_addr;
 #pragma unroll
           for (int k4 = 0; k4 < WG_BK / 16; ++k4) {
@@ -137,78 +135,136 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
             uint64_t dn = smem_desc_sw128(n_addr + k4 * 2048, 1024, WG_GROUP_BYTES);
             umma_bf16(tmem_base + (uint32_t)(t * K.ntpad), dm, dn, idesc, (blk > 0 || k4 > 0) ? 1u : 0u);
           }
-          umma_commit(&emptyA[sa]);
         }
-        umma_commit(&emptyG[sg]);
+        umma_commit(&empty[s]);
       }
       umma_commit(done);
     }
   } else {
     // =============================================================== loader warps
+    // All index arithmetic is 32-bit and INCREMENTAL: each thread computes the (sample, row, column) of its first
+    // pixel once (the only divisions of the kernel) and then walks it forward by one pass / one 64-pixel block with
+    // compare-and-carry steps — per-chunk 64-bit divisions made the first version of this loop ALU-bound.
     const bf16* dyb = reinterpret_cast<const bf16*>(P.g.dy);
     const bf16* zb = reinterpret_cast<const bf16*>(P.g.z);
     const bf16* ab = reinterpret_cast<const bf16*>(P.a.raw);
-    const int HW = P.H * P.W;
+    const int H = P.H, W = P.W, HW = P.H * P.W;
+    const int mbi = (int)mb, mei = (int)me;
     // fixed (channel chunk, first pixel row) of this thread in the G tile and in the A tile
     const int CWg = g_cw >> 3, CWa = a_cw >> 3;
     const int rppG = WG_LOAD_THREADS / CWg, rppA = WG_LOAD_THREADS / CWa;
     const int cG = tid % CWg, rG = tid / CWg, cA = tid % CWa, rA = tid / CWa;
     const bool actG = rG < rppG, actA = rA < rppA;
-    const int passG = (WG_BK + rppG - 1) / rppG, passA = (WG_BK + rppA - 1) / rppA;
     const int gch = g_c0 + cG * 8, ach = a_c0 + cA * 8;
+    const bool is_ct = P.mode == S2LC_CONVT_FWD;
     int g_q = 0, g_co = gch;                              // convT: G channel = (2x2 child q, co)
-    if (P.mode == S2LC_CONVT_FWD) { g_q = gch / P.Cout; g_co = gch - g_q * P.Cout; }
-    float gp[8], gq[8], gt[8], asc[8], ash[8];
+    if (is_ct) { g_q = gch / P.Cout; g_co = gch - g_q * P.Cout; }
+    const int g_qy = g_q >> 1, g_qx = g_q & 1;
     const bool g_aff = zb != nullptr, a_aff = P.a.scale != nullptr, a_gate = P.a.gate != nullptr;
-    if (g_aff && actG) { wg_ld8(P.g.p + g_co, gp); wg_ld8(P.g.q + g_co, gq); wg_ld8(P.g.t + g_co, gt); }
-    if (a_aff && actA) { wg_ld8(P.a.scale + ach, asc); wg_ld8(P.a.shift + ach, ash); }
+    const bool g_rs = P.g.rowscale != nullptr;
     const int a_act = P.a.act;
+    const bool a_xf = a_aff || a_gate || a_act != S2LC_ACT_NONE;
     const bool do_bias = P.dbias != nullptr && (K.g_on_m ? nti == 0 : mt == 0);
+    const bool g_xf = g_aff || g_rs || do_bias;
+    const bool g_pos = is_ct || g_rs, a_pos = TAPS == 9 || a_gate;   // who needs (n, h, w)
     float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    // steps of the coordinate walk
+    const int blkH = WG_BK / W, blkW = WG_BK - blkH * W;
+    const int pgH = rppG / W, pgW = rppG - pgH * W, paH = rppA / W, paW = rppA - paH * W;
+    auto walk = [&](int& n, int& h, int& w, int dh, int dw) {
+      w += dw;
+      if (w >= W) { w -= W; ++h; }
+      h += dh;
+      while (h >= H) { h -= H; ++n; }
+    };
+    int gn0 = 0, gh0 = 0, gw0 = 0, an0 = 0, ah0 = 0, aw0 = 0;   // coordinates of this thread's pass-0 pixel
+    {
+      int m = mbi + rG;
+      gn0 = m / HW; int r = m - gn0 * HW; gh0 = r / W; gw0 = r - gh0 * W;
+      m = mbi + rA;
+      an0 = m / HW; r = m - an0 * HW; ah0 = r / W; aw0 = r - ah0 * W;
+    }
 
     for (int blk = 0; blk < nblk; ++blk) {
-      const int64_t px0 = mb + (int64_t)blk * WG_BK;
-      // ------------------------------------------------------------ G tile
+      const int px0 = mbi + blk * WG_BK;
+      const int s = blk % K.stages;
+      unsigned char* dstG = smem + s * stage_bytes;
+      unsigned char* dstA = dstG + K.gsz;
+      // ---------------------------------------------------------- issue every load of this pixel block
+      uint4 rdy[MAXPG], rz[MAXPG], ra[TAPS][MAXPA];
+      uint32_t okG = 0, okA = 0;
       {
-        const int sg = blk % K.SG;
-        if (blk >= K.SG) mbar_wait(&emptyG[sg], (uint32_t)((blk / K.SG - 1) & 1));
-        unsigned char* dst = ringG + sg * K.gsz;
-        uint4 rdy[WG_MAXP], rz[WG_MAXP];
-        int nn[WG_MAXP];
+        int n = gn0, h = gh0, w = gw0;
 #pragma unroll
-        for (int p = 0; p < WG_MAXP; ++p) {
-          rdy[p] = make_uint4(0, 0, 0, 0); rz[p] = make_uint4(0, 0, 0, 0); nn[p] = -1;
+        for (int p = 0; p < MAXPG; ++p) {
+          rdy[p] = make_uint4(0, 0, 0, 0);
+          rz[p] = make_uint4(0, 0, 0, 0);
           const int k = rG + p * rppG;
-          const int64_t m = px0 + k;
-          if (p < passG && actG && k < WG_BK && m < me) {
-            int n = (int)(m / HW);
+          const int m = px0 + k;
+          if (actG && k < WG_BK && m < mei) {
             int64_t row = m;
-            if (P.mode == S2LC_CONVT_FWD) {
-              int rem = (int)(m - (int64_t)n * HW), h = rem / P.W, w = rem - h * P.W;
-              row = ((int64_t)n * (2 * P.H) + 2 * h + (g_q >> 1)) * (2 * P.W) + 2 * w + (g_q & 1);
-            }
-            nn[p] = n;
+            if (is_ct) row = ((int64_t)(n * 2 * H + 2 * h + g_qy)) * (2 * W) + 2 * w + g_qx;
+            okG |= 1u << p;
             rdy[p] = wg_ldg(dyb + row * P.g.ld_dy + g_co);
             if (g_aff) rz[p] = wg_ldg(zb + row * P.g.ld_z + g_co);
           }
+          if (g_pos) walk(n, h, w, pgH, pgW);
         }
+      }
+      {
+        int n = an0, h = ah0, w = aw0;
 #pragma unroll
-        for (int p = 0; p < WG_MAXP; ++p) {
+        for (int p = 0; p < MAXPA; ++p) {
+          const int k = rA + p * rppA;
+          const int m = px0 + k;
+          const bool in = actA && k < WG_BK && m < mei;
+          const bf16* src = ab + (int64_t)m * P.a.ld + ach;
+#pragma unroll
+          for (int t = 0; t < TAPS; ++t) {
+            ra[t][p] = make_uint4(0, 0, 0, 0);
+            if (TAPS == 9) {
+              const int dy = t / 3 - 1, dx = t % 3 - 1;
+              const int hh = h + dy, ww = w + dx;
+              if (in && hh >= 0 && hh < H && ww >= 0 && ww < W) {
+                okA |= 1u << (t * MAXPA + p);
+                ra[t][p] = wg_ldg(src + (int64_t)(dy * W + dx) * P.a.ld);
+              }
+            } else if (in) {
+              okA |= 1u << p;
+              ra[t][p] = wg_ldg(src);
+            }
+          }
+          if (a_pos) walk(n, h, w, paH, paW);
+        }
+      }
+      // ---------------------------------------------------------- stage free?  transform + store everything
+      if (blk >= K.stages) mbar_wait(&empty[s], (uint32_t)((blk / K.stages - 1) & 1));
+      {
+        int n = gn0, h = gh0, w = gw0;
+#pragma unroll
+        for (int p = 0; p < MAXPG; ++p) {
           const int k = rG + p * rppG;
-          if (p < passG && actG && k < WG_BK) {
-            if (nn[p] >= 0 && (g_aff || P.g.rowscale || do_bias)) {
+          if (actG && k < WG_BK) {
+            if (((okG >> p) & 1u) && g_xf) {
               float v[8];
               wg_unpack(rdy[p], v);
-              if (P.g.rowscale) {
-                float rs = __ldg(P.g.rowscale + nn[p]);
+              if (g_rs) {
+                float rs = __ldg(P.g.rowscale + n);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[j] *= rs;
               }
               if (g_aff) {
-                float z[8];
+                float z[8], c[8];
                 wg_unpack(rz[p], z);
+                wg_ld8(P.g.q + g_co, c);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = fmaf(gp[j], v[j], fmaf(gq[j], z[j], gt[j]));
+                for (int j = 0; j < 8; ++j) z[j] *= c[j];
+                wg_ld8(P.g.t + g_co, c);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) z[j] += c[j];
+                wg_ld8(P.g.p + g_co, c);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = fmaf(c[j], v[j], z[j]);
               }
               if (do_bias) {
 #pragma unroll
@@ -216,75 +272,50 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
               }
               rdy[p] = wg_pack(v);
             }
-            *reinterpret_cast<uint4*>(dst + wg_off(k, cG)) = rdy[p];
+            *reinterpret_cast<uint4*>(dstG + wg_off(k, cG)) = rdy[p];
           }
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&fullG[sg]);
-      }
-      // ------------------------------------------------------------ A tiles (one per tap)
-      int an[WG_MAXP], ah[WG_MAXP], aw[WG_MAXP];
-#pragma unroll
-      for (int p = 0; p < WG_MAXP; ++p) {
-        an[p] = -1; ah[p] = 0; aw[p] = 0;
-        const int k = rA + p * rppA;
-        const int64_t m = px0 + k;
-        if (p < passA && actA && k < WG_BK && m < me) {
-          int n = (int)(m / HW);
-          int rem = (int)(m - (int64_t)n * HW);
-          an[p] = n; ah[p] = rem / P.W; aw[p] = rem - ah[p] * P.W;
+          if (g_rs) walk(n, h, w, pgH, pgW);
         }
       }
-      for (int t = 0; t < K.taps; ++t) {
-        const int ia = blk * K.taps + t, sa = ia % K.SA;
-        if (ia >= K.SA) mbar_wait(&emptyA[sa], (uint32_t)((ia / K.SA - 1) & 1));
-        unsigned char* dst = ringA + sa * K.asz;
-        const int dy = K.taps == 9 ? t / 3 - 1 : 0, dx = K.taps == 9 ? t % 3 - 1 : 0;
-        uint4 raw[WG_MAXP];
-        bool ok[WG_MAXP];
+      {
+        int n = an0, h = ah0, w = aw0;
 #pragma unroll
-        for (int p = 0; p < WG_MAXP; ++p) {
-          raw[p] = make_uint4(0, 0, 0, 0);
-          ok[p] = false;
-          if (p < passA && an[p] >= 0) {
-            int hh = ah[p] + dy, ww = aw[p] + dx;
-            if (hh >= 0 && hh < P.H && ww >= 0 && ww < P.W) {
-              ok[p] = true;
-              raw[p] = wg_ldg(ab + (((int64_t)an[p] * P.H + hh) * P.W + ww) * P.a.ld + ach);
-            }
-          }
-        }
-#pragma unroll
-        for (int p = 0; p < WG_MAXP; ++p) {
+        for (int p = 0; p < MAXPA; ++p) {
           const int k = rA + p * rppA;
-          if (p < passA && actA && k < WG_BK) {
-            if (ok[p] && (a_aff || a_gate || a_act != S2LC_ACT_NONE)) {
-              float v[8];
-              wg_unpack(raw[p], v);
-              if (a_aff) {
+          if (actA && k < WG_BK) {
+            float sc[8], sh[8], gt8[8];
+            if (a_aff) { wg_ld8(P.a.scale + ach, sc); wg_ld8(P.a.shift + ach, sh); }
+            if (a_gate) wg_ld8(P.a.gate + (int64_t)n * P.Cin + ach, gt8);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], asc[j], ash[j]);
-              }
-              if (a_act != S2LC_ACT_NONE) {
+            for (int t = 0; t < TAPS; ++t) {
+              if (((okA >> (t * MAXPA + p)) & 1u) && a_xf) {
+                float v[8];
+                wg_unpack(ra[t][p], v);
+                if (a_aff) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j], a_act);
-              }
-              if (a_gate) {
-                float g[8];
-                wg_ld8(P.a.gate + (int64_t)an[p] * P.Cin + ach, g);
+                  for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], sc[j], sh[j]);
+                }
+                if (a_act != S2LC_ACT_NONE) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] *= g[j];
+                  for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j], a_act);
+                }
+                if (a_gate) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) v[j] *= gt8[j];
+                }
+                ra[t][p] = wg_pack(v);
               }
-              raw[p] = wg_pack(v);
+              *reinterpret_cast<uint4*>(dstA + t * K.asz + wg_off(k, cA)) = ra[t][p];
             }
-            *reinterpret_cast<uint4*>(dst + wg_off(k, cA)) = raw[p];
           }
+          if (a_gate) walk(n, h, w, paH, paW);
         }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&fullA[sa]);
       }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
+      if (g_pos) walk(gn0, gh0, gw0, blkH, blkW);
+      if (a_pos) walk(an0, ah0, aw0, blkH, blkW);
     }
 
     // =============================================================== epilogue (same warps)
@@ -294,8 +325,8 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
       const int q = warp & 3, half = warp >> 2;
       const int mrow = q * 32 + lane;
       const int nchunks = K.ntpad / 16;
-      for (int t = 0; t < K.taps; ++t) {
-        for (int cj = half; cj < nchunks; cj += WG_LOAD_WARPS / 4) {
+      for (int t = 0; t < TAPS; ++t) {
+        for (int cj = half; cj < nchunks; cj += WG_LOAD_WARPS / 4) {   // 4 warps share a TMEM lane quarter
           float acc[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * K.ntpad + cj * 16), acc);
 #pragma unroll
@@ -362,17 +393,11 @@ int32_t launch_wgrad_tc(const WgradArgs& A, cudaStream_t st) {
   const int n_side_bytes = (K.nt + 63) / 64 * WG_GROUP_BYTES;
   K.gsz = K.g_on_m ? 2 * WG_GROUP_BYTES : n_side_bytes;
   K.asz = K.g_on_m ? n_side_bytes : 2 * WG_GROUP_BYTES;
-  const int budget = 200 * 1024;
-  if (K.taps == 9) {
-    K.SG = 2;
-    K.SA = (budget - K.SG * K.gsz) / K.asz;
-    if (K.SA > 18) K.SA = 18;
-  } else {
-    int s = budget / (K.gsz + K.asz);
-    if (s > WG_MAX_SG) s = WG_MAX_SG;
-    K.SG = K.SA = s;
-  }
-  if (K.SG < 2 || K.SA < 2) return 1;
+  const int budget = 208 * 1024;
+  const int stage_bytes = K.gsz + K.taps * K.asz;
+  K.stages = budget / stage_bytes;
+  if (K.stages > 4) K.stages = 4;
+  if (K.stages < 2) return 1;
   K.tmem_cols = 32;
   while (K.tmem_cols < K.taps * K.ntpad) K.tmem_cols *= 2;
   if (K.tmem_cols > 512) return 1;
@@ -393,12 +418,14 @@ int32_t launch_wgrad_tc(const WgradArgs& A, cudaStream_t st) {
   K.px_per_slab = ((nblocks + best_slabs - 1) / best_slabs) * WG_BK;
   K.slabs = (int)((M + K.px_per_slab - 1) / K.px_per_slab);
 
-  const size_t smem = 1024 + (size_t)K.SG * K.gsz + (size_t)K.SA * K.asz +
-                      (2 * WG_MAX_SG + 2 * WG_MAX_SA + 1) * sizeof(uint64_t) + 2 * sizeof(uint32_t) +
-                      256 * sizeof(float) + 64;
+  const size_t smem = 1024 + (size_t)K.stages * stage_bytes + (2 * WG_MAX_STAGES + 1) * sizeof(uint64_t) +
+                      2 * sizeof(uint32_t) + 256 * sizeof(float) + 64;
+  auto k9 = wgrad_tc_kernel<9, 2, 1>;   // 512 loader threads: 128-ch G tile = 2 passes, <=64-ch A tile = 1 pass
+  auto k1 = wgrad_tc_kernel<1, 4, 4>;   // up to 256-ch tiles = 4 passes
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(k9, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("wgrad_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return S2LC_ERR_CUDA;
@@ -406,7 +433,10 @@ int32_t launch_wgrad_tc(const WgradArgs& A, cudaStream_t st) {
     attr_set = true;
   }
   dim3 grid((unsigned)K.slabs, (unsigned)tiles);
-  wgrad_tc_kernel<<<grid, WG_THREADS, smem, st>>>(A, K);
+  if (K.taps == 9)
+    k9<<<grid, WG_THREADS, smem, st>>>(A, K);
+  else
+    k1<<<grid, WG_THREADS, smem, st>>>(A, K);
   return check_launch("wgrad_tc");
 }
 
