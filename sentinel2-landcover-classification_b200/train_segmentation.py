@@ -82,6 +82,27 @@ class SegmentationStep:
         return loss
 
 
+class BucketReducer:
+    """Averages contiguous buckets of one flat fp32 gradient buffer across the ranks of a process group.
+    NCCL reduces with AVG in one collective; gloo (CPU tests) has no AVG, so it sums and divides."""
+
+    def __init__(self, flat_grad: torch.Tensor, buckets, process_group=None) -> None:
+        self.flat_grad, self.buckets, self.pg = flat_grad, buckets, process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.avg_native = dist.is_initialized() and dist.get_backend(process_group) == "nccl"
+
+    def reduce(self, bucket_index: int) -> None:
+        if self.world == 1:
+            return
+        a, b = self.buckets[bucket_index][:2]
+        view = self.flat_grad[a:b]
+        if self.avg_native:
+            dist.all_reduce(view, op=dist.ReduceOp.AVG, group=self.pg)
+        else:
+            dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.pg)
+            view.div_(self.world)
+
+
 class DataParallelTrainer(SegmentationStep):
     """N ranks, one process per GPU; gradients averaged with bucketed NCCL all-reduce overlapped with backward."""
 
@@ -95,18 +116,18 @@ class DataParallelTrainer(SegmentationStep):
         self.comm_stream = torch.cuda.Stream() if net_is_cuda(net) else None
         self.buckets = make_buckets(self.eng.grad_offsets, {k: p.numel() for k, p in self.eng.used},
                                     self.eng.flat_grad.numel(), self.bucket_bytes // 4)
+        self.reducer = BucketReducer(self.eng.flat_grad, self.buckets, self.pg)
         self.eng.bucket_hook = self._bucket_ready if self.world > 1 else None
         self.eng.buckets = self.buckets
         if self.world > 1:   # identical initial weights on every rank (DDP broadcasts rank 0's at construction)
             dist.broadcast(self.optimizer.flat_param, src=0, group=self.pg)
 
     def _bucket_ready(self, bucket_index: int) -> None:
-        a, b = self.buckets[bucket_index][:2]
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self.comm_stream.wait_event(ev)
         with torch.cuda.stream(self.comm_stream):
-            dist.all_reduce(self.eng.flat_grad[a:b], op=dist.ReduceOp.AVG, group=self.pg)
+            self.reducer.reduce(bucket_index)
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         loss = self.forward_backward(x, y)

@@ -121,16 +121,17 @@ def test_state_dict_roundtrip(state_shapes):
 
 
 def test_training_curve_matches_reference(golden_meta):
-    """100 steps of Adam(lr=1e-3, wd=0.05) on one fixed batch vs the curves of the LIVE reference (fp32 AND fp64,
-    tests/golden/make_curve_noise.py).  Adam's sign-like updates amplify rounding-level differences, so the
-    reference's own fp32 run drifts from its fp64 run by 7 % within 20 steps and by >50 % after ~55 steps; the
-    envelope per step is therefore max(3 %, 3x the reference's own |fp32 - fp64| deviation) while the reference is
-    still deterministic to within 10 % (the first ~50 steps), and a factor-3 band on the geometric-mean loss after
-    that (both reference curves sit inside it)."""
+    """100 steps of Adam(lr=1e-3, wd=0.05) on one fixed batch vs the curves of the LIVE reference
+    (tests/golden/make_curve_noise.py).  Adam's sign-like updates amplify rounding-level differences: six fp32 runs
+    of the reference itself whose weights were perturbed by 1e-6 (relative) spread by 1 % after 10 steps, 7 % at
+    step 17 and 21 % at step 18, and its fp32 and fp64 runs part ways completely after ~55 steps.  The per-step
+    envelope is therefore max(3 %, 2x the reference's own perturbation spread so far) while that spread is < 25 %,
+    and a factor-3 band on the geometric-mean loss of the remaining steps (both reference curves sit inside it)."""
     import math
     from s2lc_b200.losses import FocalLoss
     from _parity import alpha_weights
     r32, r64 = golden_meta["curve100_b0_224_adam1e-3_f32"], golden_meta["curve100_b0_224_adam1e-3_f64"]
+    spread = golden_meta["curve50_b0_224_adam1e-3_perturbed_maxdev"]
     model, _ = build_model("b0", "fp32")
     opt = torch.optim.Adam(model.parameters(), lr=1e-3, weight_decay=0.05)
     fn = FocalLoss(alpha_weights(), 2.0, 0.0, ignore_index=0)
@@ -142,20 +143,21 @@ def test_training_curve_matches_reference(golden_meta):
         loss.backward()
         opt.step()
         ours.append(float(loss.detach()))
-    noise = 0.0
-    checked = 0
-    for step in range(100):
-        noise = max(noise, abs(r32[step] - r64[step]) / abs(r64[step]))      # running max: drift accumulates
-        if noise > 0.10:
+    assert all(math.isfinite(v) for v in ours)
+    noise, checked = 0.0, 0
+    for step in range(len(spread)):
+        noise = max(noise, spread[step])                 # running max: drift accumulates
+        if noise > 0.25:
             break
-        tol = max(3e-2, 3 * noise)
+        tol = max(3e-2, 2 * noise)
         assert abs(ours[step] - r32[step]) <= tol * abs(r32[step]) + 1e-4, (step, ours[step], r32[step], tol)
         checked += 1
-    assert checked >= 30, checked
+    assert checked >= 15, checked
+    for step in range(10):                               # before any amplification: tight
+        assert abs(ours[step] - r32[step]) <= 3e-2 * abs(r32[step]), (step, ours[step], r32[step])
     gm = lambda c: math.exp(sum(math.log(max(v, 1e-9)) for v in c[checked:]) / (100 - checked))   # noqa: E731
     lo, hi = min(gm(r32), gm(r64)) / 3, max(gm(r32), gm(r64)) * 3
     assert lo <= gm(ours) <= hi, (gm(ours), gm(r32), gm(r64))
-    assert all(math.isfinite(v) for v in ours)
 
 
 def test_cpu_tensor_is_rejected():

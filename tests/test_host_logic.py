@@ -1,0 +1,173 @@
+"""Host-side logic that needs no GPU: the C ABI surface, the launch-list builder (dry run), the gradient buckets
+and the 2-rank data-parallel gradient averaging over gloo."""
+import os
+import re
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from s2lc_b200 import _lib, synthetic
+from s2lc_b200.efficientnet_unet import EfficientNetConfig, EfficientnetUnet, architecture
+from s2lc_b200.train_segmentation import BucketReducer, make_buckets
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "s2lc.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(s2lc_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_cabi_exports_every_declared_symbol():
+    """libs2lc.so loads on a CPU-only box and exports exactly what include/s2lc.h declares (no compute calls)."""
+    lib = _lib.load()
+    declared = _declared_symbols()
+    assert len(declared) >= 25
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/s2lc.h but not exported"
+    assert set(_lib.EXPORTED_SYMBOLS) == set(declared), set(_lib.EXPORTED_SYMBOLS) ^ set(declared)
+    assert lib.s2lc_version() >= 100
+    assert lib.s2lc_last_error() is not None
+
+
+def test_cabi_struct_layouts_match_header(tmp_path):
+    """The ctypes mirrors in _lib.py have the size and field offsets a C compiler derives from include/s2lc.h."""
+    import ctypes as C
+    import subprocess
+    structs = {"s2lc_lazy": _lib.Lazy, "s2lc_lazygrad": _lib.LazyGrad, "s2lc_conv_params": _lib.ConvParams,
+               "s2lc_wgrad_params": _lib.WgradParams}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{ROOT}/include/s2lc.h"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'  printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-std=c11", "-o", str(exe), str(src)])
+    got = dict(l.split() for l in subprocess.check_output([str(exe)], text=True).splitlines())
+    for cname, cls in structs.items():
+        assert int(got[cname]) == C.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(cls, fname).offset, f"{cname}.{fname}"
+
+
+def _model(version="b0"):
+    cfg = EfficientNetConfig(version=version, in_channels=6, num_classes=4,
+                             class_distribution=list(synthetic.CLASS_DISTRIBUTION))
+    return EfficientnetUnet(cfg)
+
+
+@pytest.mark.parametrize("version,nblocks,stem,head", [("b0", 16, 32, 1280), ("b5", 39, 48, 2048), ("b7", 55, 64, 2560)])
+def test_architecture_table(version, nblocks, stem, head):
+    """Block list generation (reference efficientnet_unet.py:184-228): counts and the b5 stage table of SURVEY.md §8."""
+    cfg = EfficientNetConfig(version=version, in_channels=6, num_classes=4)
+    s, blocks, h = architecture(cfg)
+    assert (s, len(blocks), h) == (stem, nblocks, head)
+    if version == "b5":
+        got = [(b.c_in, b.c_exp, b.kernel, b.stride, b.c_out, b.c_se) for b in blocks]
+        assert got[0] == (48, 48, 3, 1, 24, 12) and got[1] == (24, 24, 3, 1, 24, 6)
+        assert got[3] == (24, 144, 3, 2, 40, 6) and got[8] == (40, 240, 5, 2, 64, 10)
+        assert got[-1] == (512, 3072, 3, 1, 512, 128)
+
+
+def test_engine_dry_run_builds_launch_lists():
+    """The whole forward/backward launch list is built without touching a GPU; every used parameter's gradient is
+    written by exactly one backward launch and laid out in reverse execution order."""
+    from s2lc_b200._engine import Engine
+    model = _model("b0")
+    eng = Engine(model, dry_run=True)
+    x = torch.zeros(2, 6, 64, 64)
+    ws = eng.workspace(x, torch.bfloat16, True, True)
+    assert len(ws.fwd_list) == len(ws.fwd_meta) and len(ws.bwd_list) == len(ws.bwd_meta)
+    assert len(ws.fwd_list) > 150 and len(ws.bwd_list) > 200
+    used = dict(model.used_parameters())
+    assert set(ws._grad_write_idx) == set(used)
+    assert not any(k.startswith("encoder.fc.") for k in used)
+    assert eng.flat_grad.numel() >= sum(p.numel() for p in used.values())
+    # reverse execution order: the classifier's gradient sits at offset 0, the stem's at the end
+    assert eng.grad_offsets["out_conv1x1.bias"] == 0
+    assert eng.grad_offsets["encoder.stem.0.weight"] == max(eng.grad_offsets.values())
+    with pytest.raises(RuntimeError):
+        ws.run_forward(x)
+    # algorithmic flops of the forward convs agree with the per-tile figure of SURVEY.md §8 (b0 @64x64 is tiny;
+    # just require positive, finite metadata on every conv launch)
+    for label, nbytes, flops, desc in ws.fwd_meta + ws.bwd_meta:
+        assert nbytes >= 0 and flops >= 0
+
+
+def test_bucket_schedule_covers_every_bucket_once():
+    from s2lc_b200._engine import Engine
+    model = _model("b0")
+    eng = Engine(model, dry_run=True)
+    ws = eng.workspace(torch.zeros(1, 6, 64, 64), torch.bfloat16, True, True)
+    numels = {k: p.numel() for k, p in eng.used}
+    buckets = make_buckets(eng.grad_offsets, numels, eng.flat_grad.numel(), 1 << 18)
+    assert buckets[0][0] == 0 and buckets[-1][1] == eng.flat_grad.numel()
+    assert all(a[1] == b[0] for a, b in zip(buckets, buckets[1:]))
+    assert sorted(k for _, _, ks in buckets for k in ks) == sorted(numels)
+    sched = ws.bucket_schedule(buckets)
+    fired = [b for i in sorted(sched) for b in sched[i]]
+    assert sorted(fired) == list(range(len(buckets)))
+    # bucket b may fire only after the last launch that writes one of its gradients
+    for i, bs in sched.items():
+        for b in bs:
+            assert i == max(ws._grad_write_idx[k] for k in buckets[b][2])
+    # buckets complete in order (decoder first), so the all-reduce of bucket 0 overlaps the rest of backward
+    # at the production granularity (a handful of buckets) they complete in order, decoder first, so the
+    # all-reduce of bucket 0 overlaps the rest of backward
+    coarse = make_buckets(eng.grad_offsets, numels, eng.flat_grad.numel(), eng.flat_grad.numel() // 4)
+    sched = ws.bucket_schedule(coarse)
+    first_ready = {b: i for i, bs in sched.items() for b in bs}
+    assert all(first_ready[b] <= first_ready[b + 1] for b in range(len(coarse) - 1))
+    assert first_ready[0] < len(ws.bwd_list) // 2
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _dp_worker(rank: int, world: int, port: int, ret) -> None:
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        offsets = {"a": 0, "b": 12, "c": 40, "d": 44}
+        numels = {"a": 10, "b": 27, "c": 4, "d": 20}
+        total = 64
+        buckets = make_buckets(offsets, numels, total, 16)
+        g = torch.Generator().manual_seed(100 + rank)
+        flat = torch.randn(total, generator=g)
+        mine = flat.clone()
+        red = BucketReducer(flat, buckets)
+        for b in range(len(buckets)):         # the order the backward launch list fires them in
+            red.reduce(b)
+        gathered = [torch.zeros(total) for _ in range(world)]
+        dist.all_gather(gathered, mine)
+        want = torch.stack(gathered).mean(0)
+        ret[rank] = float((flat - want).abs().max())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gradient_average_gloo():
+    """DDP semantics of the trainer's exchange step: after all buckets are reduced every rank holds
+    the MEAN of the per-rank flat gradients.  world_size 2 over gloo on CPU."""
+    world, port = 2, _free_port()
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_dp_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert len(ret) == world and all(v < 1e-6 for v in ret.values()), dict(ret)
+
+
+def test_make_buckets_sizes():
+    offsets = {f"p{i}": i * 100 for i in range(10)}
+    numels = {f"p{i}": 100 for i in range(10)}
+    b = make_buckets(offsets, numels, 1000, 250)
+    assert [(x[0], x[1]) for x in b] == [(0, 300), (300, 600), (600, 900), (900, 1000)]
