@@ -175,6 +175,13 @@ def main() -> None:
 
     for _ in range(a.warmup):
         trainer(x, y)
+    eng = model.engine()
+    ws = next(w for pool in eng.workspaces.values() for w in pool if w.need_grad)
+    agg, top = None, None
+    if not a.no_breakdown:   # extra instrumented warm-up step: per-class times, picks the dominant kernel class
+        agg = kernel_breakdown(trainer, model, ws, x, y)
+        top = max(agg.items(), key=lambda kv: kv[1][1])[0]
+        eng.timing_hook = {"fwd": [], "bwd": [], "only": {top}}
     # ---- device-resident throughput
     sampler = ClockSampler(local)
     barrier()
@@ -188,6 +195,7 @@ def main() -> None:
     barrier()
     ms = e0.elapsed_time(e1) / a.steps
     clocks = sampler.stop() if rank == 0 else None
+    hook, eng.timing_hook = eng.timing_hook, None
     # ---- end to end: host buffers in, loss out, every step
     barrier()
     t0 = time.perf_counter()
@@ -206,8 +214,6 @@ def main() -> None:
     out = None
     if rank == 0:
         pk, pk_kind = peaks()
-        eng = model.engine()
-        ws = next(w for pool in eng.workspaces.values() for w in pool if w.need_grad)
         launches = len(ws.fwd_list) + len(ws.bwd_list) + len(eng.packs.get(ws.dtype, {})) + 3
         out = {
             "metric": "train_tiles_per_s", "value": a.batch * world / (ms / 1e3), "unit": "tiles/s", "n_gpus": world,
@@ -223,8 +229,9 @@ def main() -> None:
             "gpu_launches": launches * a.steps,
             "clocks": clocks,
         }
-        if not a.no_breakdown:
-            out.update(kernel_breakdown(trainer, model, ws, x, y, pk, pk_kind))
+        if agg is not None:
+            out["roofline"] = roofline_of(top, ws, hook["fwd"], hook["bwd"], a.steps, pk, pk_kind, ms)
+            out["kernel_breakdown"] = breakdown_table(agg)
         if world == 1 and not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(a)
     if world > 1:
@@ -234,9 +241,9 @@ def main() -> None:
         print(json.dumps(out))
 
 
-def kernel_breakdown(trainer, model, ws, x, y, pk, pk_kind) -> dict:
-    """One instrumented step: CUDA events around every launch of the forward/backward launch lists (on the launching
-    stream), aggregated per kernel class -> roofline of the dominant class + a per-class table."""
+def kernel_breakdown(trainer, model, ws, x, y) -> dict:
+    """One instrumented warm-up step: CUDA events around every launch of the forward/backward launch lists (on the
+    launching stream), aggregated per kernel class.  Returns {label: [launches, ms, algorithmic bytes, flops]}."""
     ev_f, ev_b = [], []
     eng = model.engine()
     hook, eng.bucket_hook = getattr(eng, "bucket_hook", None), None
@@ -250,28 +257,61 @@ def kernel_breakdown(trainer, model, ws, x, y, pk, pk_kind) -> dict:
     torch.cuda.synchronize()
     agg: dict[str, list] = {}
     for metas, evs in ((ws.fwd_meta, ev_f), (ws.bwd_meta, ev_b)):
-        for (label, nbytes, flops, _desc), (e0, e1) in zip(metas, evs):
+        for e0, e1, i in evs:
+            label, nbytes, flops, _desc = metas[i]
             r = agg.setdefault(label, [0, 0.0, 0.0, 0.0])
             r[0] += 1
             r[1] += e0.elapsed_time(e1)
             r[2] += nbytes
             r[3] += flops
+    return agg
+
+
+def breakdown_table(agg: dict) -> list:
     total_ms = sum(r[1] for r in agg.values())
     rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
-    table = [{"kernel": k, "launches": r[0], "ms": round(r[1], 3), "share": round(r[1] / total_ms, 4),
-              "GBps": round(r[2] / r[1] / 1e6, 1) if r[1] > 0 else None,
-              "TFLOPs": round(r[3] / r[1] / 1e9, 2) if r[1] > 0 else None} for k, r in rows[:12]]
-    k, r = rows[0]
-    gbps, tf = r[2] / r[1] / 1e6, r[3] / r[1] / 1e9
-    frac_hbm, frac_tc = gbps / pk["hbm_gbs"], tf / pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+    return [{"kernel": k, "launches": r[0], "ms": round(r[1], 3), "share": round(r[1] / total_ms, 4),
+             "GBps": round(r[2] / r[1] / 1e6, 1) if r[1] > 0 else None,
+             "TFLOPs": round(r[3] / r[1] / 1e9, 2) if r[1] > 0 else None} for k, r in rows[:12]]
+
+
+# kernel-class label -> CUDA kernel behind it (for the ncu cross-reference in profiles/)
+KERNEL_OF = {"conv1x1_wgrad": "wgrad_tc_kernel<1,4,4>", "conv3x3_wgrad": "wgrad_tc_kernel<9,2,1>",
+             "convT_wgrad": "wgrad_tc_kernel<1,4,4>", "conv3x3": "conv_tc_kernel", "conv3x3_dgrad": "conv_tc_kernel",
+             "conv1x1": "conv_tc_kernel", "conv1x1_dgrad": "conv_tc_kernel", "dwconv_fwd": "dwconv_kernel<MODE=0>",
+             "dwconv_bwd_data": "dwconv_kernel<MODE=1> / dwconv_bwd_data_s2_kernel",
+             "dwconv_bwd_weight": "dwconv_bwd_weight_kernel"}
+
+
+def roofline_of(label: str, ws, events_f: list, events_b: list, steps: int, pk: dict, pk_kind: str, step_ms: float) -> dict:
+    """Roofline of the dominant kernel class from the events recorded around ITS launches inside the timed region."""
+    n, ms, nbytes, flops = 0, 0.0, 0.0, 0.0
+    for metas, evs in ((ws.fwd_meta, events_f), (ws.bwd_meta, events_b)):
+        for e0, e1, i in evs:
+            n += 1
+            ms += e0.elapsed_time(e1)
+            nbytes += metas[i][1]
+            flops += metas[i][2]
+    gbps, tf = nbytes / ms / 1e6, flops / ms / 1e9
+    tpeak = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])     # timed inside a long step: sustained figure
+    frac_hbm, frac_tc = gbps / pk["hbm_gbs"], tf / tpeak
     if frac_tc > frac_hbm:
-        roof = {"bound": "tensor", "achieved": tf, "peak": pk.get("bf16_tflops_sustained", pk["bf16_tflops"]),
-                "unit": "TFLOP/s", "frac": frac_tc}
+        roof = {"bound": "tensor", "achieved": tf, "peak": tpeak, "unit": "TFLOP/s", "frac": frac_tc}
     else:
         roof = {"bound": "hbm", "achieved": gbps, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": frac_hbm}
-    roof.update({"kernel": k, "launches_per_step": r[0], "avg_launch_ms": r[1] / r[0], "peak_source": pk_kind,
-                 "traffic": None, "step_kernel_ms": total_ms})
-    return {"roofline": roof, "kernel_breakdown": table}
+    traffic = None
+    prof = os.path.join(ROOT, "profiles", "top_kernel_traffic.json")
+    if os.path.exists(prof):
+        with open(prof) as f:
+            t = json.load(f)
+        if t.get("kernel_class") == label:
+            traffic = t.get("dram_bytes_per_launch")
+    roof.update({"kernel": label, "cuda_kernel": KERNEL_OF.get(label, label), "launches_per_step": n // max(steps, 1),
+                 "avg_launch_ms": ms / max(n, 1), "algorithmic_bytes_per_launch": nbytes / max(n, 1),
+                 "algorithmic_flops_per_launch": flops / max(n, 1), "share_of_step": ms / max(steps, 1) / step_ms,
+                 "peak_source": pk_kind, "traffic": traffic,
+                 "timing": "CUDA events around each launch of this class on the launching stream, inside the timed region"})
+    return roof
 
 
 def cpu_baseline(a) -> dict:

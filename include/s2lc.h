@@ -176,6 +176,15 @@ int32_t s2lc_se_bwd_apply(void* da, int64_t ld_da, const s2lc_lazy* in, const fl
 int32_t s2lc_conv_fwd(const s2lc_conv_params* p, void* stream);
 int32_t s2lc_conv_wgrad(const s2lc_wgrad_params* p, void* stream);
 
+/* ---- classifier out_conv1x1 (C -> num_classes in 2..8, bias): efficientnet_unet.py:121,137.  Per-pixel kernels:
+ * forward  logits = W . in + b;  backward (one pass)  dW += dlogits (x) in, db += dlogits,
+ * dz = (W^T dlogits) * act'(in) with the BatchNorm-backward moments of dz accumulated into stats[2*C].  */
+int32_t s2lc_outconv_fwd(const s2lc_lazy* in, const float* w, const float* bias, void* logits, int64_t ld_out,
+                         int64_t rows, int32_t C, int32_t n_classes, int32_t dtype, void* stream);
+int32_t s2lc_outconv_bwd(const s2lc_lazy* in, const void* dlogits, int64_t ld_dl, const float* w, float* dw,
+                         float* dbias, void* dz, int64_t ld_dz, double* stats, int64_t rows, int32_t C,
+                         int32_t n_classes, int32_t dtype, void* stream);
+
 /* ---- plumbing ---------------------------------------------------------------------------------- */
 int32_t s2lc_copy_slice(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int64_t rows, int32_t C,
                         int32_t dtype, void* stream);

@@ -71,6 +71,7 @@ class Engine:
         self._param_ptrs = self._ptr_signature()
         self.weights_dirty = True
         self.direct_grad = False   # DataParallelTrainer: leave grads in flat_grad instead of returning clones
+        self.timing_hook = None    # {"fwd": [], "bwd": [], "only": {kernel-class labels}} — see Workspace.run_forward
 
     def _ptr_signature(self) -> int:
         return hash(tuple(p.data_ptr() for _, p in self.model.named_parameters()))
@@ -485,8 +486,16 @@ class Workspace:
         ncls = oc.out_channels
         self.ncls = ncls
         self.logits = self.act(N * H * W, ncls)
-        wout = pack_1x1("out_conv1x1", oc.weight)
-        self.conv(self.fwd_list, L.CONV_1X1, dec_in, N, H, W, dec_in_c, wout, self.logits, ncls, bias=oc.bias)
+        lpp = dec_in_c // 8
+        self.fused_outconv = dec_in_c % 8 == 0 and 1 <= lpp <= 32 and lpp & (lpp - 1) == 0 and 2 <= ncls <= 8
+        if self.fused_outconv:       # per-pixel HBM-bound kernel (N = num_classes is not a tensor-core shape)
+            self.F("s2lc_outconv_fwd", C.byref(dec_in), oc.weight.data_ptr(), oc.bias.data_ptr(),
+                   self.logits.data_ptr(), ncls, N * H * W, dec_in_c, ncls, self.dt)
+            self.meta(self.fwd_meta, N * H * W * (dec_in_c + ncls) * self.es, 2.0 * N * H * W * dec_in_c * ncls,
+                      f"{N}x{H}x{W} {dec_in_c}->{ncls}")
+        else:
+            wout = pack_1x1("out_conv1x1", oc.weight)
+            self.conv(self.fwd_list, L.CONV_1X1, dec_in, N, H, W, dec_in_c, wout, self.logits, ncls, bias=oc.bias)
 
         self.stats_f_arena = torch.zeros(max(self._stats_f_total, 1), dtype=torch.float64, device=self.dev)
         self.blocks, self.levels = blocks, levels      # kept for introspection (tools/diag_inter.py)
@@ -498,13 +507,20 @@ class Workspace:
         rows_top = N * H * W
         self.dlogits_g = self.lazygrad(0, ncls)     # pointer patched per call
         top = levels[-1]
-        self.wgrad(L.CONV_1X1, top.a2, self.dlogits_g, N, H, W, top.co, ncls, self.gptr("out_conv1x1.weight"),
-                   self.gptr("out_conv1x1.bias"))
-        wout_d = pack_1x1_d("out_conv1x1", oc.weight)
+        self.dlogits_ptr = C.c_void_p(0)              # patched per call (fused classifier backward)
         dyB = self.act(rows_top, top.co)
-        zB_lazy = top.a2
-        self.conv(self.bwd_list, L.CONV_1X1, self.dlogits_g, N, H, W, ncls, wout_d, dyB, top.co, prev=zB_lazy,
-                  stats=("SB", top.bnB.st_b), stats_kind=L.STATS_BNBWD)
+        if self.fused_outconv:
+            gw, gb = self.gptr("out_conv1x1.weight"), self.gptr("out_conv1x1.bias")
+            self.B("s2lc_outconv_bwd", C.byref(top.a2), self.dlogits_ptr, ncls, oc.weight.data_ptr(), gw, gb,
+                   dyB.data_ptr(), top.co, ("SB", top.bnB.st_b), rows_top, top.co, ncls, self.dt)
+            self.meta(self.bwd_meta, rows_top * (2 * top.co + ncls) * self.es, 4.0 * rows_top * top.co * ncls,
+                      f"{N}x{H}x{W} {ncls}->{top.co}")
+        else:
+            self.wgrad(L.CONV_1X1, top.a2, self.dlogits_g, N, H, W, top.co, ncls, self.gptr("out_conv1x1.weight"),
+                       self.gptr("out_conv1x1.bias"))
+            wout_d = pack_1x1_d("out_conv1x1", oc.weight)
+            self.conv(self.bwd_list, L.CONV_1X1, self.dlogits_g, N, H, W, ncls, wout_d, dyB, top.co, prev=top.a2,
+                      stats=("SB", top.bnB.st_b), stats_kind=L.STATS_BNBWD)
         for j in range(n_levels - 1, -1, -1):
             lv = levels[j]
             dcv = lv.dcv
@@ -669,7 +685,10 @@ class Workspace:
                 obj.stats = fix(obj._stats_marker)
 
     # ---------------------------------------------------------------- execution
-    def run_forward(self, x: torch.Tensor, events: list | None = None) -> torch.Tensor:
+    def run_forward(self, x: torch.Tensor, events: list | None = None, only: set | None = None) -> torch.Tensor:
+        """``events``: list that receives one (start, stop) CUDA-event pair per launch (recorded on the launching
+        stream); ``only``: restrict that to the launches whose kernel-class label is in the set (cheap enough to
+        leave on inside a timed region)."""
         if self.eng.dry_run:
             raise RuntimeError("dry-run engine cannot execute")
         st = torch.cuda.current_stream().cuda_stream
@@ -679,8 +698,11 @@ class Workspace:
         if self.training:
             L.check(lib.s2lc_memset_zero(self.stats_f_arena.data_ptr(), self.stats_f_arena.numel() * 8, st))
         self.eng.repack(self.dtype, st)
-        for fn, args in self.fwd_list:
-            if events is not None:
+        if events is None and self.eng.timing_hook is not None:
+            events, only = self.eng.timing_hook["fwd"], self.eng.timing_hook["only"]
+        for i, (fn, args) in enumerate(self.fwd_list):
+            timed = events is not None and (only is None or self.fwd_meta[i][0] in only)
+            if timed:
                 e0 = torch.cuda.Event(enable_timing=True)
                 e0.record()
             if fn == "DC":
@@ -689,10 +711,10 @@ class Workspace:
                 rc = fn(*args, st)
                 if rc:
                     L.check(rc)
-            if events is not None:
+            if timed:
                 e1 = torch.cuda.Event(enable_timing=True)
                 e1.record()
-                events.append((e0, e1))
+                events.append((e0, e1, i))
         if self.training and self.n_bn_trained:
             torch._foreach_add_(self.n_bn_trained, 1)
         n, h, w = self.N, self.H, self.W
@@ -719,26 +741,30 @@ class Workspace:
             self._bucket_sched[key] = sched
         return self._bucket_sched[key]
 
-    def run_backward(self, dlogits_nhwc: torch.Tensor, events: list | None = None) -> None:
+    def run_backward(self, dlogits_nhwc: torch.Tensor, events: list | None = None, only: set | None = None) -> None:
         st = torch.cuda.current_stream().cuda_stream
         lib = self.lib
         L.check(lib.s2lc_memset_zero(self.stats_b_arena.data_ptr(), self.stats_b_arena.numel() * 8, st))
         fg = self.eng.flat_grad
         L.check(lib.s2lc_memset_zero(fg.data_ptr(), fg.numel() * 4, st))
         self.dlogits_g.dy = dlogits_nhwc.data_ptr()
+        self.dlogits_ptr.value = dlogits_nhwc.data_ptr()
         hook = getattr(self.eng, "bucket_hook", None)
         sched = self.bucket_schedule(self.eng.buckets) if hook is not None else None
+        if events is None and self.eng.timing_hook is not None:      # bench.py: time one kernel class in the timed region
+            events, only = self.eng.timing_hook["bwd"], self.eng.timing_hook["only"]
         for i, (fn, args) in enumerate(self.bwd_list):
-            if events is not None:
+            timed = events is not None and (only is None or self.bwd_meta[i][0] in only)
+            if timed:
                 e0 = torch.cuda.Event(enable_timing=True)
                 e0.record()
             rc = fn(*args, st)
             if rc:
                 L.check(rc)
-            if events is not None:
+            if timed:
                 e1 = torch.cuda.Event(enable_timing=True)
                 e1.record()
-                events.append((e0, e1))
+                events.append((e0, e1, i))
             if sched is not None and i in sched:
                 for b in sched[i]:
                     hook(b)

@@ -70,6 +70,8 @@ _PROTOS = {
     "s2lc_se_bwd_apply": ([vp, i64, C.POINTER(Lazy), vp, vp, i32, i32, i32, i32, vp], i32),
     "s2lc_conv_fwd": ([C.POINTER(ConvParams), vp], i32),
     "s2lc_conv_wgrad": ([C.POINTER(WgradParams), vp], i32),
+    "s2lc_outconv_fwd": ([C.POINTER(Lazy), vp, vp, vp, i64, i64, i32, i32, i32, vp], i32),
+    "s2lc_outconv_bwd": ([C.POINTER(Lazy), vp, i64, vp, vp, vp, vp, i64, vp, i64, i32, i32, i32, vp], i32),
     "s2lc_copy_slice": ([vp, i64, vp, i64, i64, i32, i32, vp], i32),
     "s2lc_add_slice": ([vp, i64, vp, i64, vp, i64, i64, i32, i32, vp], i32),
     "s2lc_nchw_to_slice": ([vp, vp, i64, i32, i32, i32, i32, i32, i32, vp], i32),

@@ -317,6 +317,48 @@ def test_wgrad_lazy_operands(lib, prec, mode, cin, cout, n, h, w):
         assert rel_err(db, g.sum((0, 2, 3))) < (5e-5 if prec == "fp32" else 2e-3)
 
 
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("c,ncls,n,h,w", [(32, 4, 2, 40, 24), (32, 2, 1, 17, 9), (64, 8, 1, 16, 16)])
+def test_outconv_fused(lib, prec, c, ncls, n, h, w):
+    """Classifier 1x1 conv (+bias) on a lazy BatchNorm+ReLU input: forward, and the one-pass backward
+    (dW, db, dz with ReLU', BatchNorm-backward moments of dz) against autograd."""
+    dtype, dt, tol = DT[prec]
+    z = mk((n, c, h, w), 61)
+    wt = mk((ncls, c, 1, 1), 62, 1 / math.sqrt(c))
+    bias = 0.1 * mk((ncls,), 63)
+    sc, sh = 1 + 0.1 * mk((c,), 64), 0.1 * mk((c,), 65)
+    zr = nhwc(z, dtype)
+    zq = nchw(zr, n, h, w)
+    u = zq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1)
+    a = F.relu(u)
+    if dtype == torch.bfloat16:
+        a = a.to(dtype).float()
+    a.requires_grad_(True)
+    wq = wt.clone().requires_grad_(True)
+    bq = bias.clone().requires_grad_(True)
+    ref = F.conv2d(a, wq, bq)
+    rows = n * h * w
+    out = torch.empty(rows, ncls, dtype=dtype, device="cuda")
+    lz = lazy(zr, c, sc, sh, act=2)
+    L().check(lib.s2lc_outconv_fwd(C.byref(lz), wt.data_ptr(), bias.data_ptr(), out.data_ptr(), ncls, rows, c, ncls, dt,
+                                   stream()))
+    assert rel_err(nchw(out, n, h, w), ref) < tol
+    dl = mk((n, ncls, h, w), 66)
+    dlr = nhwc(dl, dtype)
+    gw, gb, ga = torch.autograd.grad(ref, [wq, bq, a], nchw(dlr, n, h, w))
+    dw, db = torch.zeros_like(wt), torch.zeros(ncls, device="cuda")
+    dz = torch.empty(rows, c, dtype=dtype, device="cuda")
+    st = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    L().check(lib.s2lc_outconv_bwd(C.byref(lz), dlr.data_ptr(), ncls, wt.data_ptr(), dw.data_ptr(), db.data_ptr(),
+                                   dz.data_ptr(), c, st.data_ptr(), rows, c, ncls, dt, stream()))
+    want = ga * (u > 0)
+    got = nchw(dz, n, h, w)
+    assert rel_err(dw, gw) < tol and rel_err(db, gb) < tol
+    assert rel_err(got, want) < tol
+    assert rel_err(st[:c], got.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(st[c:], (got.double() * zq.double()).sum((0, 2, 3))) < 1e-5
+
+
 # ----------------------------------------------------------------------------------------------- stem
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("h,w,co", [(64, 64, 48), (30, 34, 32)])

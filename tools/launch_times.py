@@ -53,8 +53,8 @@ def main() -> None:
         ws.run_backward(lg.grad.permute(0, 2, 3, 1).contiguous(), events=ev_b)
         torch.cuda.synchronize()
         for tag, metas, evs in (("F", ws.fwd_meta, ev_f), ("B", ws.bwd_meta, ev_b)):
-            for i, (m, (e0, e1)) in enumerate(zip(metas, evs)):
-                acc.setdefault((tag, i), [m, []])[1].append(e0.elapsed_time(e1))
+            for e0, e1, i in evs:
+                acc.setdefault((tag, i), [metas[i], []])[1].append(e0.elapsed_time(e1))
     rows = []
     for (tag, i), (m, ts) in acc.items():
         ms = sorted(ts)[len(ts) // 2]
