@@ -304,13 +304,20 @@ class Workspace:
             o, i = wt.shape[0], wt.shape[1]
             return pk(key + "/d", lambda: PackedWeight(wt, dt, 1, i, 1, o, 0, 1, 0, i))
 
-        def pack_3x3(key, wt, cbuf):  # [O, I, 3, 3]
-            o, i = wt.shape[0], wt.shape[1]
-            return pk(key + "/f", lambda: PackedWeight(wt, dt, 1, o, 9, i, 0, i * 9, 1, 9, cpad=_up(cbuf, 8)))
+        def cpad3(c, width):
+            """Per-tap K stride of a packed 3x3 weight: whole 64-channel chunks where the streaming engine
+            (csrc/sconv_tc.cu: rows that are a multiple of 128 px wide, <= 128 channels) can take the layer."""
+            return _up(c, 64) if (width % 128 == 0 and c <= 128) else _up(c, 8)
 
-        def pack_3x3_d(key, wt, n_in):
+        def pack_3x3(key, wt, cbuf, width):  # [O, I, 3, 3]
             o, i = wt.shape[0], wt.shape[1]
-            return pk(key + "/d", lambda: PackedWeight(wt, dt, 1, n_in, 9, o, 0, 9, 1, i * 9, flip=True))
+            cp = cpad3(cbuf, width)
+            return pk(f"{key}/f{cp}", lambda: PackedWeight(wt, dt, 1, o, 9, i, 0, i * 9, 1, 9, cpad=cp))
+
+        def pack_3x3_d(key, wt, n_in, width):
+            o, i = wt.shape[0], wt.shape[1]
+            cp = cpad3(o, width)
+            return pk(f"{key}/d{cp}", lambda: PackedWeight(wt, dt, 1, n_in, 9, o, 0, 9, 1, i * 9, flip=True, cpad=cp))
 
         def pack_ct(key, wt):  # [I, O, 2, 2]
             i, o = wt.shape[0], wt.shape[1]
@@ -466,8 +473,8 @@ class Workspace:
             lv.co = co
             lv.zc1, lv.zc2 = self.act(lv.rows, co), self.act(lv.rows, co)
             lv.bnA, lv.bnB = _BN(self, dcv[1], lv.rows), _BN(self, dcv[4], lv.rows)
-            lv.wA = pack_3x3(lv.kdc + ".0", dcv[0].weight, lv.c_buf)
-            lv.wB = pack_3x3(lv.kdc + ".3", dcv[3].weight, co)
+            lv.wA = pack_3x3(lv.kdc + ".0", dcv[0].weight, lv.c_buf, lv.w)
+            lv.wB = pack_3x3(lv.kdc + ".3", dcv[3].weight, co, lv.w)
             lv.cat_lazy = self.lazy(lv.cat, lv.c_buf)
             self.conv(self.fwd_list, L.CONV_3X3, lv.cat_lazy, N, lv.h, lv.w, lv.c_buf, lv.wA, lv.zc1, co,
                       bias=dcv[0].bias, stats=self.stats_f(lv.bnA),
@@ -533,7 +540,7 @@ class Workspace:
                        self.gptr(lv.kdc + ".3.bias"))
             dyA = self.act(lv.rows, co)
             lv.dyA, lv.dyB = dyA, dyB
-            wB_d = pack_3x3_d(lv.kdc + ".3", dcv[3].weight, co)
+            wB_d = pack_3x3_d(lv.kdc + ".3", dcv[3].weight, co, lv.w)
             self.conv(self.bwd_list, L.CONV_3X3, gB, N, lv.h, lv.w, co, wB_d, dyA, co, prev=lv.a1,
                       stats=("SB", lv.bnA.st_b), stats_kind=L.STATS_BNBWD)
             self.bn_backward(lv.bnA, lv.kdc + ".1")
@@ -543,7 +550,7 @@ class Workspace:
             n_in_used = lv.c_up if lv.last else lv.c_cat    # d(input tile) is not needed
             lv.c_dcat = _up(n_in_used, 8)
             lv.dcat = self.act(lv.rows, lv.c_dcat)
-            wA_d = pack_3x3_d(lv.kdc + ".0", dcv[0].weight, n_in_used)
+            wA_d = pack_3x3_d(lv.kdc + ".0", dcv[0].weight, n_in_used, lv.w)
             self.conv(self.bwd_list, L.CONV_3X3, gA, N, lv.h, lv.w, co, wA_d, lv.dcat, lv.c_dcat)
             # transposed conv: weight/bias gradient and data gradient into the level below
             gup = self.lazygrad(lv.dcat, lv.c_dcat)

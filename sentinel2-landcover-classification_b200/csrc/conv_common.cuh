@@ -169,6 +169,7 @@ __device__ __forceinline__ int64_t wgrad_index(const WgradArgs& P, int n, int k)
 int32_t launch_conv_simt(const ConvArgs& A, cudaStream_t st);
 int32_t launch_wgrad_simt(const WgradArgs& A, cudaStream_t st);
 int32_t launch_conv_tc(const ConvArgs& A, cudaStream_t st);      // igemm_tc.cu; returns 1 if shape not taken
+int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st);     // sconv_tc.cu (streaming engine); returns 1 if shape not taken
 int32_t launch_wgrad_tc(const WgradArgs& A, cudaStream_t st);
 
 }  // namespace s2lc

@@ -96,7 +96,7 @@ def main() -> None:
         x = rnd(rows, cb)
         wt = torch.randn(cout, cin, 3 if taps == 9 else 1, 3 if taps == 9 else 1, device=dev) * 0.05
         if taps == 9:
-            pw = PackedWeight(wt, bf, 1, cout, 9, cin, 0, cin * 9, 1, 9, cpad=cb)
+            pw = PackedWeight(wt, bf, 1, cout, 9, cin, 0, cin * 9, 1, 9, cpad=((cb + 63) // 64 * 64 if (w % 128 == 0 and cb <= 128) else cb))
         else:
             pw = PackedWeight(wt, bf, 1, cout, 1, cin, 0, cin, 0, 1)
         L.check(lib.s2lc_weight_pack(*pw.args, st))
