@@ -11,17 +11,18 @@
 //         pixel p on 128-byte line p of a SWIZZLE_128B K-major tile, so (dy, dx) = (slot of row r+dy, line offset dx+1)
 //         (the hardware swizzle is a function of absolute smem address bits, so no descriptor base offset is needed).
 //   1x1 : one tile of 128 consecutive pixels per ring slot.
-// Roles (544 threads):
-//   warps 0-7   producers: cp.async (16 B, straight to the swizzled destination — no staging copy, no registers),
+// Roles (512 threads):
+//   warps 0-6   producers: cp.async (16 B, straight to the swizzled destination — no staging copy, no registers),
 //               prefetching `pf` slots ahead; when a slot has landed each thread transforms ITS OWN chunks in place
 //               (BatchNorm scale/shift + SiLU/ReLU + SE gate, or the BatchNorm-backward affine p*dy + q*z + t with z
 //               staged beside it), fence.proxy.async, arrive on the slot's `full` mbarrier;
-//   warp 8      MMA issuer: one lane issues tcgen05.mma for all taps / K chunks of an output tile into one of `nacc`
+//   warp 7      MMA issuer: one lane issues tcgen05.mma for all taps / K chunks of an output tile into one of `nacc`
 //               TMEM accumulators; tcgen05.commit frees the oldest ring slot and publishes the accumulator;
-//   warps 9-16  two epilogue groups (alternate tiles): tcgen05.ld -> bias, residuals, act'(prev), bf16 store, BatchNorm
+//   warps 8-15  two epilogue groups (alternate 16-column chunks): tcgen05.ld -> bias, residuals, act'(prev), bf16 store, BatchNorm
 //               moments (butterfly column sums -> smem -> fp64 global atomics once per unit).
 // Packed weights of the CTA's N slice stay resident in shared memory for the whole kernel.
 #include <cstdlib>
+#include <type_traits>
 
 #include "conv_common.cuh"
 #include "tc_common.cuh"
@@ -30,7 +31,7 @@ namespace s2lc {
 
 using namespace tc;
 
-constexpr int SC_PROD_WARPS = 8;
+constexpr int SC_PROD_WARPS = 7;   // 7 + 1 MMA + 8 epilogue = 16 warps -> 128 registers per thread
 constexpr int SC_PROD_THREADS = SC_PROD_WARPS * 32;
 constexpr int SC_MMA_WARP = SC_PROD_WARPS;
 constexpr int SC_EPI_WARP0 = SC_PROD_WARPS + 1;
@@ -59,6 +60,9 @@ struct SPlan {
   int WS;            // 3x3: strips per image row (W / 128)
   int units;         // total units (per N slice)
   int ctas_per_slice;
+  int KS;                  // k-steps (K = 16 each) per tap
+  uint32_t koff_a[32];     // descriptor-address offsets (>> 4) of k-step s inside a slot / a weight tap
+  uint32_t koff_b[32];
 };
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
@@ -69,6 +73,11 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void sc_mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {   // one lane of the (converged) warp
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void sts16(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
@@ -165,6 +174,10 @@ struct SCursor {
   UnitGeom ug;
 };
 
+// TAPS: 9 (3x3, rolling rows) or 1 (1x1, one tile per slot).
+// REGSTAT: every epilogue group owns ONE 16-column chunk (Ncta <= 32), so BatchNorm moments accumulate in registers
+// across tiles and are reduced over the warp only when they are flushed.
+template <int TAPS, bool REGSTAT>
 __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan K) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
@@ -173,7 +186,8 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
   unsigned char* ring = wsm + K.w_bytes;                       // [ring][slot_bytes]
   unsigned char* zring = ring + K.ring * K.slot_bytes;         // [pf+1][zslot_bytes]
   float* svec = reinterpret_cast<float*>(zring + (K.pf + 1) * K.zslot_bytes);   // [3][Kc*64] operand affine vectors
-  float* sstat = svec + 3 * K.Kc * 64;                         // [2 groups][2][256]
+  float* evec = svec + 3 * K.Kc * 64;                          // [3][256] epilogue vectors: bias, prev scale, prev shift
+  float* sstat = evec + 3 * 256;                               // [2 groups][2][256]
   uint64_t* full = reinterpret_cast<uint64_t*>(sstat + 2 * 2 * 256);
   uint64_t* empty = full + SC_MAX_RING;
   uint64_t* acc_full = empty + SC_MAX_RING;
@@ -183,13 +197,15 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slice = blockIdx.x % K.nsplit, cta = blockIdx.x / K.nsplit;
   const int n0 = slice * K.Ncta;
-  const int R = K.taps == 9 ? 3 : 1;
+  constexpr int R = TAPS == 9 ? 3 : 1;
   const uint32_t ring_u32 = smem_u32(ring), w_u32 = smem_u32(wsm);
+  const int nchunks = K.Ncta / 16;
+  const int egroups = nchunks < 2 ? nchunks : 2;
 
   // ------------------------------------------------------------------ one-time setup (all threads)
   if (tid == 0) {
     for (int s = 0; s < K.ring; ++s) { mbar_init(&full[s], SC_PROD_WARPS); mbar_init(&empty[s], 1); }
-    for (int b = 0; b < K.nacc; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4); }
+    for (int b = 0; b < K.nacc; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4 * egroups); }
     fence_barrier_init();
   }
   if (warp == SC_MMA_WARP) tmem_alloc(tmem_slot, (uint32_t)K.tmem_cols);
@@ -199,12 +215,12 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
     for (int i = tid; i < nz; i += SC_THREADS) sts16(ring_u32 + (uint32_t)i * 16u, z4);
     // weights: block (tap, kc) = [Ncta rows x 128 B] SWIZZLE_128B K-major
     const bf16* wp = reinterpret_cast<const bf16*>(P.w_packed);
-    const int nw = K.taps * K.Kc * K.Ncta * 8;
+    const int nw = TAPS * K.Kc * K.Ncta * 8;
     for (int i = tid; i < nw; i += SC_THREADS) {
       const int c8 = i & 7, r = (i >> 3) % K.Ncta, blk = (i >> 3) / K.Ncta;
       const int tap = blk / K.Kc, kc = blk - tap * K.Kc;
       const int kk = tap * P.Cpad + kc * 64 + c8 * 8;
-      const bool kin = K.taps == 9 ? (kc * 64 + c8 * 8 < P.Cpad) : (kk < P.Kpad);
+      const bool kin = TAPS == 9 ? (kc * 64 + c8 * 8 < P.Cpad) : (kk < P.Kpad);
       uint4 w = z4;
       if (n0 + r < P.Npad && kin) w = __ldg(reinterpret_cast<const uint4*>(wp + (int64_t)(n0 + r) * P.Kpad + kk));
       sts16(w_u32 + (uint32_t)(blk * K.Ncta * 128) + sw128_off((uint32_t)r, (uint32_t)c8), w);
@@ -220,6 +236,13 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
         }
       }
       svec[i] = a; svec[nv + i] = b; svec[2 * nv + i] = c;
+    }
+    for (int i = tid; i < 256; i += SC_THREADS) {
+      const int col = n0 + i;
+      const bool in = i < K.Ncta && col < P.Nout;
+      evec[i] = (in && P.bias) ? P.bias[col] : 0.f;
+      evec[256 + i] = (in && P.has_prev && P.prev.scale) ? P.prev.scale[col] : 1.f;
+      evec[512 + i] = (in && P.has_prev && P.prev.scale) ? P.prev.shift[col] : 0.f;
     }
     for (int i = tid; i < 2 * 2 * 256; i += SC_THREADS) sstat[i] = 0.f;
   }
@@ -247,64 +270,84 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
     // ================================================================== producers
     const bool is_grad = P.a_is_grad != 0;
     const bf16* a_ptr = reinterpret_cast<const bf16*>(is_grad ? P.a_bwd.dy : P.a_fwd.raw);
-    const int64_t a_ld = is_grad ? P.a_bwd.ld_dy : P.a_fwd.ld;
-    const bf16* z_ptr = is_grad ? reinterpret_cast<const bf16*>(P.a_bwd.z) : nullptr;
-    const int64_t z_ld = P.a_bwd.ld_z;
+    const int a_ld = (int)(is_grad ? P.a_bwd.ld_dy : P.a_fwd.ld);
+    const bf16* z_ptr = is_grad ? reinterpret_cast<const bf16*>(P.a_bwd.z) : nullptr;   // same row stride as dy
     const float* gate = is_grad ? nullptr : P.a_fwd.gate;
     const float* rowscale = is_grad ? P.a_bwd.rowscale : nullptr;
     const int act = is_grad ? S2LC_ACT_NONE : P.a_fwd.act;
     const bool aff = is_grad ? (z_ptr != nullptr) : (P.a_fwd.scale != nullptr);
     const bool xf = aff || gate != nullptr || rowscale != nullptr || act != S2LC_ACT_NONE;
-    const int CW = K.CW, total = K.lines * CW, nv = K.Kc * 64;
-    const int line0 = tid / CW, c0 = tid - line0 * CW, dl = SC_PROD_THREADS / CW, dc = SC_PROD_THREADS - dl * CW;
+    // every ACTIVE producer thread owns one fixed 8-channel chunk `ch` (so its affine vectors live in registers) and
+    // walks the lines of a slot with stride dl
+    const int CW = K.CW, nv = K.Kc * 64;
+    const int dl = SC_PROD_THREADS / CW, nact = dl * CW;
+    const bool active = tid < nact;
+    const int line0 = tid / CW, ch = tid - line0 * CW;
+    const int nit = active ? (K.lines - line0 + dl - 1) / dl : 0;   // lines this thread owns in every slot
     const int zslots = K.pf + 1;
     const uint32_t z_u32 = smem_u32(zring);
+    const uint32_t dst_c = (uint32_t)((ch >> 3) * K.chunk_stride), ch7 = (uint32_t)(ch & 7);
+    float va[8], vb[8], vc[8];
+    {
+      const float* s0 = svec + (active ? ch * 8 : 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { va[k] = s0[k]; vb[k] = s0[nv + k]; vc[k] = s0[2 * nv + k]; }
+    }
+    int islot = 0, fslot = 0, izs = 0, fzs = 0;      // ring / z-ring positions of the issue and finish cursors
+    uint32_t iphase = 0;                              // parity to wait for on `empty` (valid once the ring wrapped)
+    bool wrapped = false;
 
-    auto slot_addr = [&](int g) { return ring_u32 + (uint32_t)((g % K.ring) * K.slot_bytes); };
-    // validity + global row of (cursor, line)
-    auto src_of = [&](const SCursor& c, int line, int64_t& row) -> bool {
-      if (K.taps == 9) {
-        const int hr = c.ug.h0 - 1 + c.j, w = c.ug.w0 - 1 + line;
-        if (hr < 0 || hr >= P.H || w < 0 || w >= P.W) return false;
-        row = ((int64_t)c.ug.n * P.H + hr) * P.W + w;
-        return true;
+    // geometry of one load: base row (pixel index of line 0), valid line range [lo, hi]
+    auto load_geom = [&](const SCursor& c, int64_t& row0, int& lo, int& hi) {
+      if (TAPS == 9) {
+        const int hr = c.ug.h0 - 1 + c.j;
+        row0 = ((int64_t)c.ug.n * P.H + hr) * P.W + c.ug.w0 - 1;
+        lo = c.ug.w0 == 0 ? 1 : 0;
+        hi = c.ug.w0 + 128 == P.W ? 128 : 129;
+        if (hr < 0 || hr >= P.H) { lo = 1; hi = 0; }   // whole row is zero padding
+      } else {
+        row0 = c.ug.m0; lo = 0; hi = 127;
       }
-      row = c.ug.m0 + line;
-      return true;
     };
     auto issue = [&](const SCursor& c) {
-      const uint32_t sa = slot_addr(c.g);
-      const uint32_t za = z_u32 + (uint32_t)((c.g % zslots) * K.zslot_bytes);
-      int line = line0, ch = c0, it = tid;
-#pragma unroll 1
-      for (int i = 0; i < SC_MAX_ITEMS && it < total; ++i) {
-        const uint32_t dst = sa + (uint32_t)((ch >> 3) * K.chunk_stride + line * 128 + (((ch & 7) ^ (line & 7)) << 4));
-        int64_t row;
-        if (src_of(c, line, row)) {
-          cp_async16(dst, a_ptr + row * a_ld + ch * 8);
-          if (z_ptr) cp_async16(za + (uint32_t)it * 16u, z_ptr + row * z_ld + ch * 8);
-        } else {
-          sts16(dst, make_uint4(0, 0, 0, 0));
+      const uint32_t sa = ring_u32 + (uint32_t)(islot * K.slot_bytes) + dst_c;
+      const uint32_t za = z_u32 + (uint32_t)(izs * K.zslot_bytes) + (uint32_t)tid * 16u;
+      int64_t row0; int lo, hi;
+      load_geom(c, row0, lo, hi);
+      const bf16* abase = a_ptr + row0 * a_ld + ch * 8;
+      const bf16* zbase = z_ptr ? z_ptr + row0 * a_ld + ch * 8 : nullptr;
+      {
+        int line = line0;
+#pragma unroll 2
+        for (int i = 0; i < nit; ++i, line += dl) {
+          const uint32_t dst = sa + (uint32_t)(line * 128) + ((ch7 ^ (uint32_t)(line & 7)) << 4);
+          if (line >= lo && line <= hi) {
+            const int off = line * a_ld;
+            cp_async16(dst, abase + off);
+            if (zbase) cp_async16(za + (uint32_t)(i * nact) * 16u, zbase + off);
+          } else {
+            sts16(dst, make_uint4(0, 0, 0, 0));
+          }
         }
-        it += SC_PROD_THREADS; line += dl; ch += dc;
-        if (ch >= CW) { ch -= CW; ++line; }
       }
       cp_async_commit();
     };
     auto finish = [&](const SCursor& c) {
-      if (xf) {
-        const uint32_t sa = slot_addr(c.g);
-        const uint32_t za = z_u32 + (uint32_t)((c.g % zslots) * K.zslot_bytes);
+      if (xf && active) {
+        const uint32_t sa = ring_u32 + (uint32_t)(fslot * K.slot_bytes) + dst_c;
+        const uint32_t za = z_u32 + (uint32_t)(fzs * K.zslot_bytes) + (uint32_t)tid * 16u;
+        int64_t row0; int lo, hi;
+        load_geom(c, row0, lo, hi);
         const float rs = rowscale ? __ldg(rowscale + c.ug.n) : 1.f;
-        int line = line0, ch = c0, it = tid;
-#pragma unroll 1
-        for (int i = 0; i < SC_MAX_ITEMS && it < total; ++i) {
-          int64_t row;
-          if (src_of(c, line, row)) {
-            const uint32_t dst = sa + (uint32_t)((ch >> 3) * K.chunk_stride + line * 128 + (((ch & 7) ^ (line & 7)) << 4));
+        float g8[8];
+        if (gate) sc_ldf8(gate + (int64_t)c.ug.n * P.C + ch * 8, g8);
+        int line = line0;
+#pragma unroll 2
+        for (int i = 0; i < nit; ++i, line += dl) {
+          if (line >= lo && line <= hi) {
+            const uint32_t dst = sa + (uint32_t)(line * 128) + ((ch7 ^ (uint32_t)(line & 7)) << 4);
             float v[8];
             sc_unpack8(lds16(dst), v);
-            const float* s0 = svec + ch * 8;
             if (is_grad) {
               if (rowscale) {
 #pragma unroll
@@ -312,35 +355,34 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
               }
               if (z_ptr) {
                 float z[8];
-                sc_unpack8(lds16(za + (uint32_t)it * 16u), z);
+                sc_unpack8(lds16(za + (uint32_t)(i * nact) * 16u), z);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) v[k] = fmaf(s0[k], v[k], fmaf(s0[nv + k], z[k], s0[2 * nv + k]));
+                for (int k = 0; k < 8; ++k) v[k] = fmaf(va[k], v[k], fmaf(vb[k], z[k], vc[k]));
               }
             } else {
               if (aff) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], s0[k], s0[nv + k]);
+                for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], va[k], vb[k]);
               }
-              if (act != S2LC_ACT_NONE) {
+              if (act == S2LC_ACT_RELU) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) v[k] = act_fwd(v[k], act);
+                for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+              } else if (act == S2LC_ACT_SILU) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = v[k] * sigmoidf_(v[k]);
               }
               if (gate) {
-                float g8[8];
-                sc_ldf8(gate + (int64_t)c.ug.n * P.C + ch * 8, g8);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) v[k] *= g8[k];
               }
             }
             sts16(dst, sc_pack8(v));
           }
-          it += SC_PROD_THREADS; line += dl; ch += dc;
-          if (ch >= CW) { ch -= CW; ++line; }
         }
       }
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) sc_mbar_arrive(&full[c.g % K.ring]);
+      if (lane == 0) sc_mbar_arrive(&full[fslot]);
     };
 
     SCursor ci, cf;
@@ -349,13 +391,14 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
     int inflight = 0;
     while (cf.ok) {
       while (ci.ok && inflight <= K.pf) {
-        if (ci.g >= K.ring) mbar_wait(&empty[ci.g % K.ring], (uint32_t)((ci.g / K.ring - 1) & 1));
+        if (wrapped) mbar_wait(&empty[islot], iphase);
         issue(ci);
         ++inflight;
         cur_next(ci);
+        if (++islot == K.ring) { islot = 0; if (wrapped) iphase ^= 1u; wrapped = true; }
+        if (++izs == zslots) izs = 0;
       }
-      // oldest group must have landed: allow (inflight - 1) younger groups to stay pending
-      switch (inflight - 1) {
+      switch (inflight - 1) {   // the oldest group must have landed; younger ones may stay in flight
         case 0: cp_async_wait<0>(); break;
         case 1: cp_async_wait<1>(); break;
         case 2: cp_async_wait<2>(); break;
@@ -364,191 +407,268 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
       finish(cf);
       --inflight;
       cur_next(cf);
+      if (++fslot == K.ring) fslot = 0;
+      if (++fzs == zslots) fzs = 0;
     }
   } else if (warp == SC_MMA_WARP) {
-    // ================================================================== MMA issuer
-    if (lane == 0) {
+    // ================================================================== MMA issuer.  The WHOLE warp walks the loop
+    // converged (so every address is warp-uniform and lives in uniform registers); one elected lane issues.
+    {
+      const bool leader = elect_one();
       const uint32_t idesc = idesc_bf16(128, (uint32_t)K.Ncta, 0, 0);
-      int t = 0, gbase = 0, gw = 0;
+      const uint64_t dbase = smem_desc_sw128(0, 1024, 16);          // address bits are added below (addr >> 4 < 2^14)
+      const uint32_t a_lo = ring_u32 >> 4, w_lo = w_u32 >> 4;
+      const uint32_t slot16 = (uint32_t)K.slot_bytes >> 4;
+      const uint32_t wblk16 = (uint32_t)(K.Ncta * 128) >> 4;        // one (tap, kc) weight block
+      int fs = 0;  uint32_t fph = 0;        // next `full` barrier to observe
+      int s_first = 0;                      // ring slot of load 0 of the current unit
+      int b = 0;   uint32_t bph = 0;  bool bwrapped = false;
       for (int u = cta; u < K.units; u += K.ctas_per_slice) {
         const UnitGeom ug = unit_geom(P, K, u);
-        for (int o = 0; o < ug.nout; ++o, ++t) {
-          const int need = gbase + o + R - 1;
-          while (gw <= need) { mbar_wait(&full[gw % K.ring], (uint32_t)((gw / K.ring) & 1)); ++gw; }
-          const int b = t % K.nacc;
-          if (t >= K.nacc) mbar_wait(&acc_empty[b], (uint32_t)((t / K.nacc - 1) & 1));
+        int waited = 0;                     // loads of this unit already observed
+        int r0 = s_first;
+        for (int o = 0; o < ug.nout; ++o) {
+          while (waited < o + R) {
+            mbar_wait(&full[fs], fph);
+            if (++fs == K.ring) { fs = 0; fph ^= 1u; }
+            ++waited;
+          }
+          if (bwrapped) mbar_wait(&acc_empty[b], bph);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)(b * K.Ncta);
           uint32_t accum = 0;
-          for (int tap = 0; tap < K.taps; ++tap) {
-            int dy1 = 0, dx1 = 0;                       // dy + 1, dx + 1
-            if (K.taps == 9) { dy1 = tap / 3; dx1 = tap - dy1 * 3; }
-            const uint32_t a_base = ring_u32 + (uint32_t)(((gbase + o + dy1) % K.ring) * K.slot_bytes + dx1 * 128);
-            for (int kc = 0; kc < K.Kc; ++kc) {
-              int rem = P.C - kc * 64;
-              rem = rem > 64 ? 64 : rem;
-              const int ks = (rem + 15) >> 4;
-              const uint32_t b_base = w_u32 + (uint32_t)((tap * K.Kc + kc) * K.Ncta * 128);
-              for (int k4 = 0; k4 < ks; ++k4) {
-                umma_bf16(d_tmem, sc_desc(a_base + (uint32_t)(kc * K.chunk_stride + k4 * 32)),
-                          smem_desc_sw128(b_base + (uint32_t)(k4 * 32), 1024, 16), idesc, accum);
+          int rs = r0;
+#pragma unroll
+          for (int dy1 = 0; dy1 < R; ++dy1) {
+            const uint32_t a_row = a_lo + (uint32_t)rs * slot16;
+#pragma unroll
+            for (int dx1 = 0; dx1 < R; ++dx1) {
+              const uint64_t a_tap = dbase + (uint64_t)(a_row + (uint32_t)(dx1 * 8));          // + dx1 lines of 128 B
+              const uint64_t b_tap = dbase + (uint64_t)(w_lo + (uint32_t)((dy1 * R + dx1) * K.Kc) * wblk16);
+#pragma unroll 2
+              for (int ks = 0; ks < K.KS; ++ks) {
+                if (leader) umma_bf16(d_tmem, a_tap + K.koff_a[ks], b_tap + K.koff_b[ks], idesc, accum);
                 accum = 1;
               }
             }
+            if (++rs == K.ring) rs = 0;
           }
-          umma_commit(&acc_full[b]);
-          umma_commit(&empty[(gbase + o) % K.ring]);
-          if (R == 3 && o == ug.nout - 1) {
-            umma_commit(&empty[(gbase + o + 1) % K.ring]);
-            umma_commit(&empty[(gbase + o + 2) % K.ring]);
+          if (leader) {
+            umma_commit(&acc_full[b]);
+            umma_commit(&empty[r0]);
+            if (R == 3 && o == ug.nout - 1) {
+              int r1 = r0 + 1 == K.ring ? 0 : r0 + 1;
+              int r2 = r1 + 1 == K.ring ? 0 : r1 + 1;
+              umma_commit(&empty[r1]);
+              umma_commit(&empty[r2]);
+            }
           }
+          __syncwarp();
+          if (++r0 == K.ring) r0 = 0;
+          if (++b == K.nacc) { b = 0; if (bwrapped) bph ^= 1u; bwrapped = true; }
         }
-        gbase += ug.nload;
+        s_first += ug.nload;
+        while (s_first >= K.ring) s_first -= K.ring;
       }
     }
   } else {
-    // ================================================================== epilogue groups
+    // ================================================================== epilogue: 2 groups x 4 lane-quarter warps;
+    // group g owns the 16-column chunks cj = g, g+2, ... of EVERY tile.
     const int ew = warp - SC_EPI_WARP0, grp = ew >> 2, q = warp & 3;   // q = TMEM lane quarter this warp may read
-    float* gstat = sstat + grp * 512;                                   // [2][256] of this group
-    const int gtid = (ew & 3) * 32 + lane;
-    const int nchunks = K.Ncta / 16;
-    bf16* outp = reinterpret_cast<bf16*>(P.out);
-    int t = 0, since_flush = 0;
-    auto flush = [&]() {
-      asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");
-      for (int i = gtid; i < K.Ncta; i += 128) {
-        if (n0 + i < P.Nout) {
-          atomicAdd(&P.stats[n0 + i], (double)gstat[i]);
-          atomicAdd(&P.stats[P.Nout + n0 + i], (double)gstat[256 + i]);
+    if (grp < egroups) {
+      float* gstat = sstat + grp * 512;                                 // [2][256] of this group
+      const int gtid = (ew & 3) * 32 + lane;
+      bf16* outp = reinterpret_cast<bf16*>(P.out);
+      const bf16* prevp = P.has_prev ? reinterpret_cast<const bf16*>(P.prev.raw) : nullptr;
+      const bf16* res1p = reinterpret_cast<const bf16*>(P.res1);
+      const bf16* res2p = reinterpret_cast<const bf16*>(P.res2);
+      const int prev_act = P.has_prev ? P.prev.act : S2LC_ACT_NONE;
+      const int r = q * 32 + lane;
+      int b = 0;  uint32_t bph = 0;
+      int since_flush = 0;
+      float rs0[16], rs1[16];                     // REGSTAT accumulators (chunk `grp`)
+#pragma unroll
+      for (int j = 0; j < 16; ++j) { rs0[j] = 0.f; rs1[j] = 0.f; }
+      auto flush = [&]() {
+        if (REGSTAT) {
+          int col;
+          const float t0 = sc_butterfly16(rs0, lane, col);
+          const float t1 = sc_butterfly16(rs1, lane, col);
+          if ((lane & 1) == 0) {
+            atomicAdd(&gstat[grp * 16 + col], t0);
+            atomicAdd(&gstat[256 + grp * 16 + col], t1);
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) { rs0[j] = 0.f; rs1[j] = 0.f; }
         }
-        gstat[i] = 0.f;
-        gstat[256 + i] = 0.f;
-      }
-      asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");
-    };
-    for (int u = cta; u < K.units; u += K.ctas_per_slice) {
-      const UnitGeom ug = unit_geom(P, K, u);
-      for (int o = 0; o < ug.nout; ++o, ++t) {
-        if ((t & 1) != grp) continue;
-        const int b = t % K.nacc;
-        mbar_wait(&acc_full[b], (uint32_t)((t / K.nacc) & 1));
-        tc_fence_after();
-        const int r = q * 32 + lane;
-        int64_t orow;
-        int n_s;
-        if (K.taps == 9) {
-          n_s = ug.n;
-          orow = ((int64_t)ug.n * P.H + ug.h0 + o) * P.W + ug.w0 + r;
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");
+        for (int i = gtid; i < K.Ncta; i += 128) {
+          const float v0 = gstat[i], v1 = gstat[256 + i];
+          if (n0 + i < P.Nout && (v0 != 0.f || v1 != 0.f)) {
+            atomicAdd(&P.stats[n0 + i], (double)v0);
+            atomicAdd(&P.stats[P.Nout + n0 + i], (double)v1);
+          }
+          gstat[i] = 0.f;
+          gstat[256 + i] = 0.f;
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");
+      };
+      const bool has_bias = P.bias != nullptr;
+      const int stats_kind = P.stats_kind;
+      // one 16-column chunk of one tile row.  FULL: all 16 columns exist (16 B vector path, no per-column predicates)
+      auto chunk = [&](auto full_tag, int lc0, int col0, int nvalid, int64_t orow, int b, float srs) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        // issue the global loads of this chunk first, then read the accumulator
+        uint4 pz0 = make_uint4(0, 0, 0, 0), pz1 = pz0, ra0 = pz0, ra1 = pz0, rb0 = pz0, rb1 = pz0;
+        if (FULL) {
+          if (prevp) {
+            const uint4* p = reinterpret_cast<const uint4*>(prevp + orow * P.prev.ld + col0);
+            pz0 = __ldg(p); pz1 = __ldg(p + 1);
+          }
+          if (res1p) {
+            const uint4* p = reinterpret_cast<const uint4*>(res1p + orow * P.ld_res1 + col0);
+            ra0 = __ldg(p); ra1 = __ldg(p + 1);
+          }
+          if (res2p) {
+            const uint4* p = reinterpret_cast<const uint4*>(res2p + orow * P.ld_res2 + col0);
+            rb0 = __ldg(p); rb1 = __ldg(p + 1);
+          }
+        }
+        float acc[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * K.Ncta + lc0), acc);
+        if (has_bias) {
+          const float4* bv = reinterpret_cast<const float4*>(evec + lc0);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 t = bv[j4];
+            acc[4 * j4] += t.x; acc[4 * j4 + 1] += t.y; acc[4 * j4 + 2] += t.z; acc[4 * j4 + 3] += t.w;
+          }
+        }
+        float zp[16];
+        if (FULL) {
+          float e[8];
+          if (res1p) {
+            sc_unpack8(ra0, e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += e[j];
+            sc_unpack8(ra1, e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[8 + j] += e[j];
+          }
+          if (res2p) {
+            sc_unpack8(rb0, e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += e[j];
+            sc_unpack8(rb1, e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[8 + j] += e[j];
+          }
+          sc_unpack8(pz0, *reinterpret_cast<float(*)[8]>(&zp[0]));
+          sc_unpack8(pz1, *reinterpret_cast<float(*)[8]>(&zp[8]));
+        } else {   // ragged last chunk: scalar path
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            zp[j] = 0.f;
+            if (j < nvalid) {
+              if (res1p) acc[j] += __bfloat162float(res1p[orow * P.ld_res1 + col0 + j]);
+              if (res2p) acc[j] += __bfloat162float(res2p[orow * P.ld_res2 + col0 + j]);
+              if (prevp) zp[j] = __bfloat162float(prevp[orow * P.prev.ld + col0 + j]);
+            }
+          }
+        }
+        if (prev_act == S2LC_ACT_RELU) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            acc[j] = fmaf(zp[j], evec[256 + lc0 + j], evec[512 + lc0 + j]) > 0.f ? acc[j] : 0.f;
+        } else if (prev_act == S2LC_ACT_SILU) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            acc[j] *= act_bwd(fmaf(zp[j], evec[256 + lc0 + j], evec[512 + lc0 + j]), S2LC_ACT_SILU);
+        }
+        // round to the stored precision (statistics must see what the consumer will read back)
+        uint4 o0, o1;
+        {
+          __nv_bfloat162* h0 = reinterpret_cast<__nv_bfloat162*>(&o0);
+          __nv_bfloat162* h1 = reinterpret_cast<__nv_bfloat162*>(&o1);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            h0[j] = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+            h1[j] = __floats2bfloat162_rn(acc[8 + 2 * j], acc[8 + 2 * j + 1]);
+          }
+        }
+        bf16* op = outp + orow * P.ld_out + col0;
+        if (FULL) {
+          *reinterpret_cast<uint4*>(op) = o0;
+          *reinterpret_cast<uint4*>(op + 8) = o1;
         } else {
-          n_s = ug.n;
-          orow = ug.m0 + r;
+          const bf16* hv0 = reinterpret_cast<const bf16*>(&o0);
+          const bf16* hv1 = reinterpret_cast<const bf16*>(&o1);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (j < nvalid) op[j] = hv0[j];
+            if (8 + j < nvalid) op[8 + j] = hv1[j];
+          }
         }
-        for (int cj = 0; cj < nchunks; ++cj) {
-          const int col0 = n0 + cj * 16;
-          int nvalid = P.Nout - col0;
-          nvalid = nvalid > 16 ? 16 : nvalid;
-          if (nvalid <= 0) break;   // warp-uniform
-          float acc[16];
-          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * K.Ncta + cj * 16), acc);
-          const bool full16 = nvalid == 16;
-          if (P.bias) {
+        if (stats_kind != S2LC_STATS_NONE) {
+          float v[16];
+          sc_unpack8(o0, *reinterpret_cast<float(*)[8]>(&v[0]));
+          sc_unpack8(o1, *reinterpret_cast<float(*)[8]>(&v[8]));
+          if (!FULL) {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-              if (j < nvalid) acc[j] += __ldg(P.bias + col0 + j);
+              if (j >= nvalid) v[j] = 0.f;
           }
-          auto add_rows = [&](const void* base, int64_t ld) {
-            const bf16* p = reinterpret_cast<const bf16*>(base) + orow * ld + col0;
-            if (full16 && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
-              float e[8];
-              sc_unpack8(__ldg(reinterpret_cast<const uint4*>(p)), e);
+          if (REGSTAT) {
+            if (stats_kind == S2LC_STATS_MOMENTS) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) acc[j] += e[j];
-              sc_unpack8(__ldg(reinterpret_cast<const uint4*>(p + 8)), e);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) acc[8 + j] += e[j];
+              for (int j = 0; j < 16; ++j) { rs0[j] += v[j]; rs1[j] = fmaf(v[j], v[j], rs1[j]); }
             } else {
 #pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (j < nvalid) acc[j] += __bfloat162float(p[j]);
+              for (int j = 0; j < 16; ++j) { const float x = v[j] * srs; rs0[j] += x; rs1[j] = fmaf(x, zp[j], rs1[j]); }
             }
-          };
-          if (P.res1) add_rows(P.res1, P.ld_res1);
-          if (P.res2) add_rows(P.res2, P.ld_res2);
-          float zp[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) zp[j] = 0.f;
-          if (P.has_prev) {
-            const bf16* p = reinterpret_cast<const bf16*>(P.prev.raw) + orow * P.prev.ld + col0;
-            if (full16 && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
-              float e[8];
-              sc_unpack8(__ldg(reinterpret_cast<const uint4*>(p)), e);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) zp[j] = e[j];
-              sc_unpack8(__ldg(reinterpret_cast<const uint4*>(p + 8)), e);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) zp[8 + j] = e[j];
-            } else {
-#pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (j < nvalid) zp[j] = __bfloat162float(p[j]);
-            }
-            if (P.prev.act != S2LC_ACT_NONE) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j)
-                if (j < nvalid) {
-                  float uu = zp[j];
-                  if (P.prev.scale) uu = fmaf(uu, __ldg(P.prev.scale + col0 + j), __ldg(P.prev.shift + col0 + j));
-                  acc[j] *= act_bwd(uu, P.prev.act);
-                }
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < 16; ++j) acc[j] = roundf_as<bf16>(acc[j]);
-          bf16* op = outp + orow * P.ld_out + col0;
-          if (full16 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-            float lo[8], hi[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) { lo[j] = acc[j]; hi[j] = acc[8 + j]; }
-            *reinterpret_cast<uint4*>(op) = sc_pack8(lo);
-            *reinterpret_cast<uint4*>(op + 8) = sc_pack8(hi);
           } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (j < nvalid) op[j] = __float2bfloat16_rn(acc[j]);
-          }
-          if (P.stats_kind != S2LC_STATS_NONE) {
             float s0[16], s1[16];
-            if (P.stats_kind == S2LC_STATS_MOMENTS) {
+            if (stats_kind == S2LC_STATS_MOMENTS) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float v = j < nvalid ? acc[j] : 0.f;
-                s0[j] = v; s1[j] = v * v;
-              }
+              for (int j = 0; j < 16; ++j) { s0[j] = v[j]; s1[j] = v[j] * v[j]; }
             } else {
-              const float rs = P.stats_rowscale ? __ldg(P.stats_rowscale + n_s) : 1.f;
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float v = j < nvalid ? acc[j] * rs : 0.f;
-                s0[j] = v; s1[j] = v * zp[j];
-              }
+              for (int j = 0; j < 16; ++j) { const float x = v[j] * srs; s0[j] = x; s1[j] = x * zp[j]; }
             }
             int col;
             const float t0 = sc_butterfly16(s0, lane, col);
             const float t1 = sc_butterfly16(s1, lane, col);
             if ((lane & 1) == 0) {
-              atomicAdd(&gstat[cj * 16 + col], t0);
-              atomicAdd(&gstat[256 + cj * 16 + col], t1);
+              atomicAdd(&gstat[lc0 + col], t0);
+              atomicAdd(&gstat[256 + lc0 + col], t1);
             }
           }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) sc_mbar_arrive(&acc_empty[b]);
-        ++since_flush;
+      };
+      for (int u = cta; u < K.units; u += K.ctas_per_slice) {
+        const UnitGeom ug = unit_geom(P, K, u);
+        int64_t orow = TAPS == 9 ? ((int64_t)ug.n * P.H + ug.h0) * P.W + ug.w0 + r : ug.m0 + r;
+        const float srs = (P.stats_kind == S2LC_STATS_BNBWD && P.stats_rowscale) ? __ldg(P.stats_rowscale + ug.n) : 1.f;
+        for (int o = 0; o < ug.nout; ++o, orow += P.W) {
+          mbar_wait(&acc_full[b], bph);
+          tc_fence_after();
+          for (int cj = grp; cj < nchunks; cj += 2) {
+            const int lc0 = cj * 16, col0 = n0 + lc0;
+            const int nvalid = P.Nout - col0;
+            if (nvalid <= 0) break;   // warp-uniform
+            if (nvalid >= 16) chunk(std::true_type{}, lc0, col0, 16, orow, b, srs);
+            else chunk(std::false_type{}, lc0, col0, nvalid, orow, b, srs);
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) sc_mbar_arrive(&acc_empty[b]);
+          if (++b == K.nacc) { b = 0; bph ^= 1u; }
+          ++since_flush;
+        }
+        if (P.stats_kind != S2LC_STATS_NONE && since_flush >= 32) { flush(); since_flush = 0; }
       }
-      if (P.stats_kind != S2LC_STATS_NONE && since_flush >= 16) { flush(); since_flush = 0; }
+      if (P.stats_kind != S2LC_STATS_NONE && since_flush > 0) flush();
     }
-    if (P.stats_kind != S2LC_STATS_NONE && since_flush > 0) flush();
   }
   tc_fence_before();
   __syncthreads();
@@ -568,12 +688,16 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
   if (A.C % 8 != 0 || A.Kpad % 64 != 0 || !sc_aligned16(A.w_packed)) return 1;
   if (A.a_is_grad) {
     if (A.a_bwd.ld_dy % 8 != 0 || !sc_aligned16(A.a_bwd.dy)) return 1;
-    if (A.a_bwd.z && (A.a_bwd.ld_z % 8 != 0 || !sc_aligned16(A.a_bwd.z))) return 1;
+    if (A.a_bwd.z && (A.a_bwd.ld_z != A.a_bwd.ld_dy || !sc_aligned16(A.a_bwd.z))) return 1;
   } else {
     if (A.a_fwd.ld % 8 != 0 || !sc_aligned16(A.a_fwd.raw)) return 1;
     if (A.a_fwd.scale && !A.a_fwd.shift) return 1;
   }
   if (A.has_prev && A.prev.scale && !A.prev.shift) return 1;
+  if (A.ld_out % 8 != 0 || !sc_aligned16(A.out)) return 1;          // the epilogue moves 16 B vectors
+  if (A.has_prev && (A.prev.ld % 8 != 0 || !sc_aligned16(A.prev.raw))) return 1;
+  if (A.res1 && (A.ld_res1 % 8 != 0 || !sc_aligned16(A.res1))) return 1;
+  if (A.res2 && (A.ld_res2 % 8 != 0 || !sc_aligned16(A.res2))) return 1;
   const int64_t HW = (int64_t)A.H * A.W, M = HW * A.N;
   SPlan K{};
   K.taps = A.mode == S2LC_CONV_3X3 ? 9 : 1;
@@ -588,22 +712,22 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
     K.lines = 128;
     K.chunk_stride = 16 * 1024;
   }
-  if ((K.lines * K.CW + SC_PROD_THREADS - 1) / SC_PROD_THREADS > SC_MAX_ITEMS) return 1;
   K.slot_bytes = K.Kc * K.chunk_stride;
   const bool has_z = A.a_is_grad && A.a_bwd.z != nullptr;
   K.zslot_bytes = has_z ? K.lines * K.CW * 16 : 0;
   const int R = K.taps == 9 ? 3 : 1;
   const int n16 = sc_up(A.Nout, 16);
   const int budget = 226 * 1024;
-  const int fixed = 1024 + 3 * K.Kc * 64 * 4 + 2 * 2 * 256 * 4 + (2 * SC_MAX_RING + 2 * SC_MAX_ACC) * 8 + 64;
+  const int fixed = 1024 + 3 * K.Kc * 64 * 4 + 3 * 256 * 4 + 2 * 2 * 256 * 4 + (2 * SC_MAX_RING + 2 * SC_MAX_ACC) * 8 + 64;
   bool found = false;
   for (int ns = 1; ns <= 4 && !found; ++ns) {
     const int ncta = sc_up((n16 + ns - 1) / ns, 16);
     if (ncta > 256) continue;
     const int wb = K.taps * K.Kc * ncta * 128;
     for (int ring = 6; ring >= R + 1; --ring) {
-      int pf = ring - R;
+      int pf = ring - R - 1;          // one slot of slack so producers never wait on the tile they just fed
       if (pf > 3) pf = 3;
+      if (pf < 1) pf = 1;
       if (fixed + wb + ring * K.slot_bytes + (pf + 1) * K.zslot_bytes <= budget) {
         K.nsplit = ns; K.Ncta = ncta; K.w_bytes = wb; K.ring = ring; K.pf = pf;
         found = true;
@@ -637,17 +761,34 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
   }
   if (K.units < ctas) ctas = K.units;
   K.ctas_per_slice = ctas;
+  K.KS = 0;
+  for (int kc = 0; kc < K.Kc; ++kc) {
+    int rem = A.C - kc * 64;
+    rem = rem > 64 ? 64 : rem;
+    for (int k4 = 0; k4 < (rem + 15) / 16; ++k4, ++K.KS) {
+      K.koff_a[K.KS] = (uint32_t)((kc * K.chunk_stride + k4 * 32) >> 4);
+      K.koff_b[K.KS] = (uint32_t)((kc * K.Ncta * 128 + k4 * 32) >> 4);
+    }
+  }
   const size_t smem = (size_t)fixed + K.w_bytes + (size_t)K.ring * K.slot_bytes + (size_t)(K.pf + 1) * K.zslot_bytes;
+  const bool regstat = K.Ncta <= 32;
+  void (*kern)(ConvArgs, SPlan) =
+      K.taps == 9 ? (regstat ? sconv_kernel<9, true> : sconv_kernel<9, false>)
+                  : (regstat ? sconv_kernel<1, true> : sconv_kernel<1, false>);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(sconv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaSuccess;
+    void (*all[4])(ConvArgs, SPlan) = {sconv_kernel<9, true>, sconv_kernel<9, false>, sconv_kernel<1, true>,
+                                       sconv_kernel<1, false>};
+    for (int i = 0; i < 4 && e == cudaSuccess; ++i)
+      e = cudaFuncSetAttribute(all[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("sconv_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return S2LC_ERR_CUDA;
     }
     attr_set = true;
   }
-  sconv_kernel<<<ctas * K.nsplit, SC_THREADS, smem, st>>>(A, K);
+  kern<<<ctas * K.nsplit, SC_THREADS, smem, st>>>(A, K);
   return check_launch("sconv_tc");
 }
 
