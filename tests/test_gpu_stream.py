@@ -110,3 +110,46 @@ def test_stream_conv1x1(lib, cin, cout, n, h, w, gated):
     (ro, rs), (go, gs) = _both(bwd)
     assert rel_err(go, ro) < 2e-3
     assert rel_err(gs, rs) < 2e-3
+
+
+def _run_wgrad(lib, mode, lz, lg, n, h, w, cin, cout, shape, bias):
+    from test_gpu_kernels import run_wgrad
+    dw = torch.zeros(shape, device="cuda")
+    db = torch.zeros(cout, device="cuda") if bias else None
+    run_wgrad(lib, 1, mode, lz, lg, n, h, w, cin, cout, dw, db)
+    return dw, (db if bias else torch.zeros(1, device="cuda"))
+
+
+@pytest.mark.parametrize("cin,cbuf,cout,n,h,w", [(38, 40, 32, 2, 12, 128), (32, 32, 32, 1, 70, 256), (88, 88, 64, 2, 10, 128),
+                                                 (64, 64, 64, 3, 5, 256), (128, 128, 64, 1, 9, 128)])
+def test_stream_wgrad3x3(lib, cin, cbuf, cout, n, h, w):
+    """3x3 weight gradient, both operands lazy (BatchNorm+ReLU on A, BatchNorm-backward affine on G) + bias gradient."""
+    rows = n * h * w
+    x = mk((rows, cbuf), 131).to(BF)
+    x[:, cin:] = 0
+    plain_a = cbuf != cin                      # the concat buffer is consumed untransformed
+    sc, sh = 1 + 0.1 * mk((cbuf,), 132), 0.1 * mk((cbuf,), 133)
+    lz = lazy(x, cbuf) if plain_a else lazy(x, cbuf, sc, sh, act=2)
+    dy, z = mk((rows, cout), 134).to(BF), mk((rows, cout), 135).to(BF)
+    p_, q_, t_ = 1 + 0.1 * mk((cout,), 136), 0.05 * mk((cout,), 137), 0.01 * mk((cout,), 138)
+    lg = lazygrad(dy, cout, z, p_, q_, t_)
+    (rw, rb), (gw, gb) = _both(lambda: _run_wgrad(lib, 1, lz, lg, n, h, w, cin, cout, (cout, cin, 3, 3), True))
+    assert rel_err(gw, rw) < 1e-3
+    assert rel_err(gb, rb) < 1e-3
+
+
+@pytest.mark.parametrize("cin,cout,n,h,w,gated", [(24, 144, 2, 144, 144, False), (144, 40, 2, 144, 144, True),
+                                                  (240, 64, 3, 128, 112, True), (64, 384, 2, 160, 128, False),
+                                                  (384, 128, 2, 144, 144, True), (48, 24, 2, 144, 144, True)])
+def test_stream_wgrad1x1(lib, cin, cout, n, h, w, gated):
+    rows = n * h * w
+    x = mk((rows, cin), 141).to(BF)
+    sc, sh = 1 + 0.1 * mk((cin,), 142), 0.1 * mk((cin,), 143)
+    gate = torch.sigmoid(mk((n, cin), 144)) if gated else None
+    lz = lazy(x, cin, sc, sh, gate, act=1)
+    dy, z = mk((rows, cout), 145).to(BF), mk((rows, cout), 146).to(BF)
+    p_, q_, t_ = 1 + 0.1 * mk((cout,), 147), 0.05 * mk((cout,), 148), 0.01 * mk((cout,), 149)
+    rsc = 0.5 + torch.rand(n, device="cuda")
+    lg = L().LazyGrad(dy.data_ptr(), cout, z.data_ptr(), cout, p_.data_ptr(), q_.data_ptr(), t_.data_ptr(), rsc.data_ptr())
+    (rw, _), (gw, _) = _both(lambda: _run_wgrad(lib, 0, lz, lg, n, h, w, cin, cout, (cout, cin, 1, 1), False))
+    assert rel_err(gw, rw) < 1e-3
