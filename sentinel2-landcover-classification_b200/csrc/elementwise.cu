@@ -247,94 +247,127 @@ __global__ void se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t l
   }
 }
 
-// one block per sample: gate = sigmoid(W2 silu(W1 pooled + b1) + b2)
-__global__ void se_fc_fwd_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
-                                 const float* __restrict__ b1, const float* __restrict__ w2,
-                                 const float* __restrict__ b2, float* __restrict__ gate, int C, int S) {
+// The squeeze-excite FCs are tiny ([N, C] x [C, S], S = C/24): what matters is spreading them over the SMs.
+// Grid = (channel blocks of 256, N); every block recomputes the S hidden units of its sample (cheap) and owns
+// 256 of the C channels.
+constexpr int SE_CB = 256;
+
+// hidden pre-activation hp[s] = W1[s, :] . x + b1[s] for one sample (x in smem), all warps of the block
+__device__ __forceinline__ void se_hidden(const float* xs, const float* __restrict__ w1, const float* __restrict__ b1,
+                                          float* hp, int C, int S) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int s = warp; s < S; s += nw) {
+    const float* wr = w1 + (int64_t)s * C;
+    float a = 0.f;
+    for (int c = lane * 4; c + 3 < C; c += 128) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(wr + c));
+      a += w.x * xs[c] + w.y * xs[c + 1] + w.z * xs[c + 2] + w.w * xs[c + 3];
+    }
+    a = warp_sum(a);
+    if (lane == 0) hp[s] = a + b1[s];
+  }
+}
+
+// gate = sigmoid(W2 silu(W1 pooled + b1) + b2)
+__global__ void __launch_bounds__(256) se_fc_fwd_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
+                                                        const float* __restrict__ b1, const float* __restrict__ w2,
+                                                        const float* __restrict__ b2, float* __restrict__ gate, int C,
+                                                        int S) {
   extern __shared__ float smem[];
   float* xs = smem;      // [C]
   float* hs = smem + C;  // [S]
-  const int n = blockIdx.x;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) xs[c] = pooled[(int64_t)n * C + c];
+  const int n = blockIdx.y, c = blockIdx.x * SE_CB + threadIdx.x;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) xs[i] = pooled[(int64_t)n * C + i];
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  for (int s = warp; s < S; s += nw) {
-    float a = 0.f;
-    for (int c = lane; c < C; c += 32) a += w1[(int64_t)s * C + c] * xs[c];
-    a = warp_sum(a);
-    if (lane == 0) hs[s] = act_fwd(a + b1[s], S2LC_ACT_SILU);
-  }
+  se_hidden(xs, w1, b1, hs, C, S);
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  for (int s = threadIdx.x; s < S; s += blockDim.x) hs[s] = act_fwd(hs[s], S2LC_ACT_SILU);
+  __syncthreads();
+  if (c < C) {
     float a = b2[c];
-    for (int s = 0; s < S; ++s) a += w2[(int64_t)c * S + s] * hs[s];
+    const float* wr = w2 + (int64_t)c * S;
+    for (int s = 0; s < S; ++s) a = fmaf(__ldg(wr + s), hs[s], a);
     gate[(int64_t)n * C + c] = sigmoidf_(a);
   }
 }
 
-// per-sample part of the SE backward: recompute h, gate; write dgp[N,C], h[N,S], dhp[N,S], dpool[N,C]
-__global__ void se_fc_bwd_sample_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
-                                        const float* __restrict__ b1, const float* __restrict__ w2,
-                                        const float* __restrict__ b2, const float* __restrict__ dgate,
-                                        float* __restrict__ dpool, float* __restrict__ sc_dgp,
-                                        float* __restrict__ sc_h, float* __restrict__ sc_dhp, int C, int S) {
+// backward, step 1: dgp[n, c] = dgate * g(1-g); hp[n, s] (pre-activation, written by channel block 0);
+// dacc[n, s] += sum over this block's channels of dgp[c] * W2[c, s]   (dacc pre-zeroed)
+__global__ void __launch_bounds__(256) se_fc_bwd1_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
+                                                         const float* __restrict__ b1, const float* __restrict__ w2,
+                                                         const float* __restrict__ b2, const float* __restrict__ dgate,
+                                                         float* __restrict__ sc_dgp, float* __restrict__ sc_hp,
+                                                         float* __restrict__ sc_dacc, int C, int S) {
   extern __shared__ float smem[];
-  float* xs = smem;            // [C] pooled
-  float* dg = smem + C;        // [C] dgp
-  float* hp = smem + 2 * C;    // [S] pre-activation
-  float* dh = smem + 2 * C + S;  // [S]
-  const int n = blockIdx.x;
+  float* xs = smem;               // [C]
+  float* hp = smem + C;           // [S] pre-activation
+  float* hs = hp + S;             // [S] silu(hp)
+  float* dg = hs + S;             // [SE_CB]
+  const int n = blockIdx.y, c0 = blockIdx.x * SE_CB, c = c0 + threadIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) xs[c] = pooled[(int64_t)n * C + c];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) xs[i] = pooled[(int64_t)n * C + i];
   __syncthreads();
-  for (int s = warp; s < S; s += nw) {
-    float a = 0.f;
-    for (int c = lane; c < C; c += 32) a += w1[(int64_t)s * C + c] * xs[c];
-    a = warp_sum(a);
-    if (lane == 0) hp[s] = a + b1[s];
+  se_hidden(xs, w1, b1, hp, C, S);
+  __syncthreads();
+  for (int s = threadIdx.x; s < S; s += blockDim.x) {
+    hs[s] = act_fwd(hp[s], S2LC_ACT_SILU);
+    if (blockIdx.x == 0) sc_hp[(int64_t)n * S + s] = hp[s];
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  float d = 0.f;
+  if (c < C) {
     float a = b2[c];
-    for (int s = 0; s < S; ++s) a += w2[(int64_t)c * S + s] * act_fwd(hp[s], S2LC_ACT_SILU);
-    float g = sigmoidf_(a);
-    float d = dgate[(int64_t)n * C + c] * g * (1.f - g);
-    dg[c] = d;
+    const float* wr = w2 + (int64_t)c * S;
+    for (int s = 0; s < S; ++s) a = fmaf(__ldg(wr + s), hs[s], a);
+    const float g = sigmoidf_(a);
+    d = dgate[(int64_t)n * C + c] * g * (1.f - g);
     sc_dgp[(int64_t)n * C + c] = d;
   }
+  dg[threadIdx.x] = d;
   __syncthreads();
+  const int cn = (C - c0) < SE_CB ? (C - c0) : SE_CB;
   for (int s = warp; s < S; s += nw) {
     float a = 0.f;
-    for (int c = lane; c < C; c += 32) a += dg[c] * w2[(int64_t)c * S + s];
+    for (int i = lane; i < cn; i += 32) a = fmaf(dg[i], __ldg(w2 + (int64_t)(c0 + i) * S + s), a);
     a = warp_sum(a);
-    if (lane == 0) {
-      float d = a * act_bwd(hp[s], S2LC_ACT_SILU);
-      dh[s] = d;
-      sc_dhp[(int64_t)n * S + s] = d;
-      sc_h[(int64_t)n * S + s] = act_fwd(hp[s], S2LC_ACT_SILU);
-    }
+    if (lane == 0) atomicAdd(&sc_dacc[(int64_t)n * S + s], a);
   }
+}
+
+// backward, step 2: dhp[s] = dacc[s] * silu'(hp[s]);  dpool[n, c] = sum_s dhp[s] * W1[s, c]
+__global__ void __launch_bounds__(256) se_fc_bwd2_kernel(const float* __restrict__ w1, const float* __restrict__ sc_hp,
+                                                         const float* __restrict__ sc_dacc, float* __restrict__ dpool,
+                                                         int C, int S) {
+  extern __shared__ float smem[];
+  float* dh = smem;  // [S]
+  const int n = blockIdx.y, c = blockIdx.x * SE_CB + threadIdx.x;
+  for (int s = threadIdx.x; s < S; s += blockDim.x)
+    dh[s] = sc_dacc[(int64_t)n * S + s] * act_bwd(sc_hp[(int64_t)n * S + s], S2LC_ACT_SILU);
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  if (c < C) {
     float a = 0.f;
-    for (int s = 0; s < S; ++s) a += dh[s] * w1[(int64_t)s * C + c];
+    for (int s = 0; s < S; ++s) a = fmaf(dh[s], __ldg(w1 + (int64_t)s * C + c), a);
     dpool[(int64_t)n * C + c] = a;
   }
 }
 
-// weight part: dw2[c,s] = sum_n dgp[n,c] h[n,s]; dw1[s,c] = sum_n dhp[n,s] pooled[n,c]; biases
-__global__ void se_fc_bwd_weight_kernel(const float* __restrict__ pooled, const float* __restrict__ sc_dgp,
-                                        const float* __restrict__ sc_h, const float* __restrict__ sc_dhp,
-                                        float* __restrict__ dw1, float* __restrict__ db1, float* __restrict__ dw2,
-                                        float* __restrict__ db2, int N, int C, int S) {
+// weight part: dw2[c,s] = sum_n dgp[n,c] silu(hp[n,s]); dw1[s,c] = sum_n dhp[n,s] pooled[n,c]; biases
+__global__ void __launch_bounds__(256) se_fc_bwd_weight_kernel(const float* __restrict__ pooled,
+                                                               const float* __restrict__ sc_dgp,
+                                                               const float* __restrict__ sc_hp,
+                                                               const float* __restrict__ sc_dacc,
+                                                               float* __restrict__ dw1, float* __restrict__ db1,
+                                                               float* __restrict__ dw2, float* __restrict__ db2, int N,
+                                                               int C, int S) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= C * S) return;
-  int c = i / S, s = i % S;
+  int s = i / C, c = i - s * C;   // consecutive threads = consecutive channels: coalesced dgp / pooled / dw1
   float a2 = 0.f, a1 = 0.f, bb2 = 0.f, bb1 = 0.f;
   for (int n = 0; n < N; ++n) {
-    float g = sc_dgp[(int64_t)n * C + c], d = sc_dhp[(int64_t)n * S + s];
-    a2 += g * sc_h[(int64_t)n * S + s];
-    a1 += d * pooled[(int64_t)n * C + c];
+    const float hpv = __ldg(sc_hp + (int64_t)n * S + s);
+    const float g = sc_dgp[(int64_t)n * C + c], d = __ldg(sc_dacc + (int64_t)n * S + s) * act_bwd(hpv, S2LC_ACT_SILU);
+    a2 = fmaf(g, act_fwd(hpv, S2LC_ACT_SILU), a2);
+    a1 = fmaf(d, pooled[(int64_t)n * C + c], a1);
     bb2 += g;
     bb1 += d;
   }
@@ -724,22 +757,32 @@ int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, f
 
 int32_t s2lc_se_fc_fwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                        float* gate, int32_t N, int32_t C, int32_t S, void* stream) {
+  S2LC_REQUIRE(C % 4 == 0, S2LC_ERR_ALIGN, "se_fc_fwd: C=%d must be a multiple of 4", C);
   size_t smem = sizeof(float) * (size_t)(C + S);
-  se_fc_fwd_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(pooled, w1, b1, w2, b2, gate, C, S);
+  dim3 grid((C + SE_CB - 1) / SE_CB, N);
+  se_fc_fwd_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(pooled, w1, b1, w2, b2, gate, C, S);
   return check_launch("se_fc_fwd");
 }
 
 int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                        const float* dgate, float* dpool, float* dw1, float* db1, float* dw2, float* db2,
                        float* scratch, int32_t N, int32_t C, int32_t S, void* stream) {
-  float* sc_dgp = scratch;
-  float* sc_h = scratch + (size_t)N * C;
-  float* sc_dhp = sc_h + (size_t)N * S;
-  size_t smem = sizeof(float) * (size_t)(2 * C + 2 * S);
-  se_fc_bwd_sample_kernel<<<N, 256, smem, (cudaStream_t)stream>>>(pooled, w1, b1, w2, b2, dgate, dpool, sc_dgp, sc_h,
-                                                                   sc_dhp, C, S);
-  se_fc_bwd_weight_kernel<<<(C * S + 255) / 256, 256, 0, (cudaStream_t)stream>>>(pooled, sc_dgp, sc_h, sc_dhp, dw1,
-                                                                                  db1, dw2, db2, N, C, S);
+  S2LC_REQUIRE(C % 4 == 0, S2LC_ERR_ALIGN, "se_fc_bwd: C=%d must be a multiple of 4", C);
+  float* sc_dgp = scratch;                       // [N, C]
+  float* sc_hp = scratch + (size_t)N * C;        // [N, S] hidden pre-activation
+  float* sc_dacc = sc_hp + (size_t)N * S;        // [N, S] sum_c dgp * W2 (accumulated atomically)
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(sc_dacc, 0, sizeof(float) * (size_t)N * S, st);
+  if (e != cudaSuccess) {
+    set_error("se_fc_bwd: memset: %s", cudaGetErrorString(e));
+    return S2LC_ERR_CUDA;
+  }
+  dim3 grid((C + SE_CB - 1) / SE_CB, N);
+  se_fc_bwd1_kernel<<<grid, 256, sizeof(float) * (size_t)(C + 2 * S + SE_CB), st>>>(pooled, w1, b1, w2, b2, dgate,
+                                                                                    sc_dgp, sc_hp, sc_dacc, C, S);
+  se_fc_bwd2_kernel<<<grid, 256, sizeof(float) * (size_t)S, st>>>(w1, sc_hp, sc_dacc, dpool, C, S);
+  se_fc_bwd_weight_kernel<<<(C * S + 255) / 256, 256, 0, st>>>(pooled, sc_dgp, sc_hp, sc_dacc, dw1, db1, dw2, db2, N,
+                                                                C, S);
   return check_launch("se_fc_bwd");
 }
 

@@ -17,6 +17,7 @@
 // channel slice of the concat buffer) and the per-channel BatchNorm moments (butterfly warp reduction).
 #include "conv_common.cuh"
 #include "tc_common.cuh"
+#include "stream_common.cuh"
 
 namespace s2lc {
 
@@ -222,17 +223,21 @@ __global__ void __launch_bounds__(TC_THREADS, 2) conv_tc_kernel(ConvArgs P, int 
     }
     fence_proxy_async();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0) {   // converged warp: descriptors stay in uniform registers, one elected lane issues
       tc_fence_after();
+      const bool leader = elect_one();
       const uint32_t a_addr = smem_u32(sa), b_addr = smem_u32(sb);
 #pragma unroll
       for (int k4 = 0; k4 < TC_BK / 16; ++k4) {
         uint64_t da = smem_desc_sw128(a_addr + k4 * 32, 1024, 16);
         uint64_t db = smem_desc_sw128(b_addr + k4 * 32, 1024, 16);
-        umma_bf16(tmem_base, da, db, idesc, (kc > 0 || k4 > 0) ? 1u : 0u);
+        if (leader) umma_bf16(tmem_base, da, db, idesc, (kc > 0 || k4 > 0) ? 1u : 0u);
       }
-      umma_commit(&bar_empty[s]);
-      if (kc == nk - 1) umma_commit(bar_done);
+      if (leader) {
+        umma_commit(&bar_empty[s]);
+        if (kc == nk - 1) umma_commit(bar_done);
+      }
+      __syncwarp();
     }
   }
 

@@ -20,6 +20,7 @@
 // Split-K over pixel slabs fills the 148 SMs; there is no CPU or library fallback.
 #include "conv_common.cuh"
 #include "tc_common.cuh"
+#include "stream_common.cuh"
 
 namespace s2lc {
 
@@ -118,8 +119,10 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
 
   if (warp == WG_LOAD_WARPS) {
     // =============================================================== MMA issuer (one elected lane)
-    if (lane == 0 && nblk > 0) {
+    if (nblk > 0) {    // converged warp: descriptors stay in uniform registers, one elected lane issues
+      const bool leader = elect_one();
       const uint32_t idesc = idesc_bf16(128, (uint32_t)K.ntpad, 1, 1);   // both operands MN-major
+      const uint64_t dbase = smem_desc_sw128(0, 1024, WG_GROUP_BYTES);
       for (int blk = 0; blk < nblk; ++blk) {
         const int s = blk % K.stages;
         mbar_wait(&full[s], (uint32_t)((blk / K.stages) & 1));
@@ -131,14 +134,16 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
           const uint32_t m_addr = K.g_on_m ? g_addr : a_addr, n_addr = K.g_on_m ? a_addr : g_addr;
 #pragma unroll
           for (int k4 = 0; k4 < WG_BK / 16; ++k4) {
-            uint64_t dm = smem_desc_sw128(m_addr + k4 * 2048, 1024, WG_GROUP_BYTES);
-            uint64_t dn = smem_desc_sw128(n_addr + k4 * 2048, 1024, WG_GROUP_BYTES);
-            umma_bf16(tmem_base + (uint32_t)(t * K.ntpad), dm, dn, idesc, (blk > 0 || k4 > 0) ? 1u : 0u);
+            const uint64_t dm = dbase + (uint64_t)((m_addr + k4 * 2048) >> 4);
+            const uint64_t dn = dbase + (uint64_t)((n_addr + k4 * 2048) >> 4);
+            if (leader) umma_bf16(tmem_base + (uint32_t)(t * K.ntpad), dm, dn, idesc, (blk > 0 || k4 > 0) ? 1u : 0u);
           }
         }
-        umma_commit(&empty[s]);
+        if (leader) umma_commit(&empty[s]);
+        __syncwarp();
       }
-      umma_commit(done);
+      if (leader) umma_commit(done);
+      __syncwarp();
     }
   } else {
     // =============================================================== loader warps
