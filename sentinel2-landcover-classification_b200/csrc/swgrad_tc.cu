@@ -45,7 +45,8 @@ struct WPlan {
   int a_slot, g_slot;  // bytes per slot
   int zslot;           // bytes per z staging slot (0: no BatchNorm behind G)
   int ringA, ringG, pf;
-  int nsplit, nt;      // 3x3: input-channel slices per unit and slice width
+  int nsplit, nt;      // CTAs per unit (= asplit * gsplit) and the A slice width in channels
+  int asplit, g_w;     // A slices; G slice width in channels (G slices = nsplit / asplit)
   int m_on_g;          // 1: G channels on M (TMEM lanes), A on N;  0: swapped
   int n_mtiles;
   int Npad;            // MMA N
@@ -107,14 +108,20 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int slice = blockIdx.x % K.nsplit, cta = blockIdx.x / K.nsplit;
-  const int a_c0 = slice * K.nt;                                   // first input channel of this CTA's A slice
+  const int a_c0 = (slice % K.asplit) * K.nt;                      // first input channel of this CTA's A slice
+  const int g_c0 = (slice / K.asplit) * K.g_w;                     // first output channel of its G slice
   constexpr int R = TAPS == 9 ? 3 : 1;
   const uint32_t ringA_u32 = smem_u32(ringA), ringG_u32 = smem_u32(ringG), z_u32 = smem_u32(zring);
   const int Ca = (P.Cin + 7) & ~7;
   int CWa = K.CWa;                                                  // chunks of this slice that exist in the buffer
-  if (TAPS == 9) {
+  {
     const int left = (Ca - a_c0) >> 3;
     CWa = left < CWa ? left : CWa;
+  }
+  int CWg_ = K.CWg;
+  {
+    const int left = (P.Cout - g_c0) >> 3;
+    CWg_ = left < CWg_ ? left : CWg_;
   }
 
   if (tid == 0) {
@@ -161,14 +168,14 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
     const int act = P.a.act;
     const bool a_aff = P.a.scale != nullptr;
     const bool a_xf = a_aff || gate != nullptr || act != S2LC_ACT_NONE;
-    const bool do_bias = P.dbias != nullptr && slice == 0;
+    const bool do_bias = P.dbias != nullptr && (slice % K.asplit) == 0;
     const bool g_xf = z_ptr != nullptr || rowscale != nullptr || do_bias;
     // fixed chunk per thread, separately for the A part and the G part of a load
     const int dla = SW_PROD_THREADS / CWa, nact_a = dla * CWa;
     const int la0 = tid / CWa, cha = tid - la0 * CWa;
     const bool act_a = tid < nact_a;
     const int nit_a = act_a ? (K.a_lines - la0 + dla - 1) / dla : 0;
-    const int CWg = K.CWg, dlg = SW_PROD_THREADS / CWg, nact_g = dlg * CWg;
+    const int CWg = CWg_, dlg = SW_PROD_THREADS / CWg, nact_g = dlg * CWg;
     const int lg0 = tid / CWg, chg = tid - lg0 * CWg;
     const bool act_g = tid < nact_g;
     const int nit_g = act_g ? (K.lines - lg0 + dlg - 1) / dlg : 0;
@@ -178,7 +185,9 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
 #pragma unroll
     for (int k = 0; k < 8; ++k) { sa[k] = 1.f; sb[k] = 0.f; gp[k] = 1.f; gq[k] = 0.f; gt[k] = 0.f; bsum[k] = 0.f; }
     if (act_a && a_aff) { sc_ldf8(P.a.scale + a_c0 + cha * 8, sa); sc_ldf8(P.a.shift + a_c0 + cha * 8, sb); }
-    if (act_g && z_ptr) { sc_ldf8(P.g.p + chg * 8, gp); sc_ldf8(P.g.q + chg * 8, gq); sc_ldf8(P.g.t + chg * 8, gt); }
+    if (act_g && z_ptr) {
+      sc_ldf8(P.g.p + g_c0 + chg * 8, gp); sc_ldf8(P.g.q + g_c0 + chg * 8, gq); sc_ldf8(P.g.t + g_c0 + chg * 8, gt);
+    }
     const int zslots = K.pf + 1;
     int ia = 0, ig = 0, iz = 0, fa = 0, fg = 0, fz = 0;     // ring positions: issue / finish cursors
     uint32_t pha = 0, phg = 0;
@@ -214,8 +223,8 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
       if (gok) {
         const uint32_t sG = ringG_u32 + (uint32_t)(ig * K.g_slot) + dst_cg;
         const uint32_t zG = z_u32 + (uint32_t)(iz * K.zslot) + (uint32_t)tid * 16u;
-        const bf16* dbase = dy_ptr + grow0 * g_ld + chg * 8;
-        const bf16* zbase = z_ptr ? z_ptr + grow0 * g_ld + chg * 8 : nullptr;
+        const bf16* dbase = dy_ptr + grow0 * g_ld + g_c0 + chg * 8;
+        const bf16* zbase = z_ptr ? z_ptr + grow0 * g_ld + g_c0 + chg * 8 : nullptr;
         line = lg0;
 #pragma unroll 2
         for (int i = 0; i < nit_g; ++i, line += dlg) {
@@ -327,7 +336,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
         for (int k = 0; k < 8; ++k) atomicAdd(&sbias[chg * 8 + k], bsum[k]);
       }
       asm volatile("bar.sync 1, %0;" ::"n"(SW_PROD_THREADS) : "memory");
-      for (int i = tid; i < P.Cout; i += SW_PROD_THREADS) atomicAdd(P.dbias + i, sbias[i]);
+      for (int i = tid; i < CWg * 8; i += SW_PROD_THREADS) atomicAdd(P.dbias + g_c0 + i, sbias[i]);
     }
   } else if (warp == SW_MMA_WARP) {
     // ================================================================== MMA issuer (converged warp, elected lane)
@@ -425,10 +434,11 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           const int nch = cj * 16 + j;
-          const int co = K.m_on_g ? mch : nch;
-          const int ci = (K.m_on_g ? nch : mch) + a_c0;
-          const bool n_in = TAPS == 9 ? nch < K.nt : true;   // columns beyond the slice belong to the next CTA
-          if (co < P.Cout && ci < P.Cin && n_in) atomicAdd(P.dw + wgrad_index(P, co, tap * P.Cin + ci), v[j]);
+          const int gl = K.m_on_g ? mch : nch, al = K.m_on_g ? nch : mch;   // channel inside the G / A slice
+          const int co = gl + g_c0, ci = al + a_c0;
+          // rows / columns beyond the slice widths belong to another CTA (and are zero here)
+          if (gl < K.g_w && al < K.nt && co < P.Cout && ci < P.Cin)
+            atomicAdd(P.dw + wgrad_index(P, co, tap * P.Cin + ci), v[j]);
         }
       }
     }
@@ -454,18 +464,17 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
   if (A.g.z && (A.g.ld_z != A.g.ld_dy || !sw_aligned16(A.g.z))) return 1;
   if (A.a.scale && (!A.a.shift || A.Cin % 8 != 0)) return 1;
   if (A.a.gate && A.Cin % 8 != 0) return 1;
-  if (A.dbias && A.Cout > 256) return 1;
   const int64_t HW = (int64_t)A.H * A.W, M = HW * A.N;
   const int budget = 226 * 1024;
   const int fixed = 1024 + 256 * 4 + (3 * SW_MAX_RING + 1) * 8 + 64;
   WPlan K{};
   K.taps = A.mode == S2LC_CONV_3X3 ? 9 : 1;
   K.CWg = A.Cout / 8;
-  if (K.CWg > SW_PROD_THREADS) return 1;
   int ctas = kNumSMs;
   if (K.taps == 9) {
     if (A.W % 128 != 0 || A.Cout > 128) return 1;
     K.nsplit = (Ca + 47) / 48;
+    K.asplit = K.nsplit; K.g_w = A.Cout;
     K.nt = sw_up((Ca + K.nsplit - 1) / K.nsplit, 8);
     K.Npad = sw_up(K.nt, 16);
     if (9 * K.Npad > 512) return 1;
@@ -501,30 +510,53 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
       if (ru >= A.H) break;
     }
   } else {
-    // the wider operand goes on M (TMEM lanes) in tiles of 128 channels, the narrower one on N
-    K.nsplit = 1; K.nt = Ca;
-    K.CWa = Ca / 8;
-    if (K.CWa > SW_PROD_THREADS) return 1;
+    // the wider operand goes on M (TMEM lanes) in tiles of 128 channels, the narrower one on N.  Deep layers do not
+    // fit one CTA's TMEM (n_mtiles * Npad <= 512 columns): the [Cm x Cn] gradient is cut into msplit x nsplit_n
+    // blocks, each block x pixel-range is one CTA.  Cost model: bytes one CTA streams.
     K.m_on_g = A.Cout >= Ca ? 1 : 0;
     const int cm = K.m_on_g ? A.Cout : Ca, cn = K.m_on_g ? Ca : A.Cout;
-    K.n_mtiles = (cm + 127) / 128;
-    K.Npad = sw_up(cn, 16);
-    K.nacc = K.n_mtiles;
-    if (K.Npad > 256 || K.nacc * K.Npad > 512) return 1;
-    const int chunks_m = 2 * K.n_mtiles, chunks_n = (K.Npad + 63) / 64;
-    const int chunks_a = K.m_on_g ? chunks_n : chunks_m, chunks_g = K.m_on_g ? chunks_m : chunks_n;
+    const int zm = (K.m_on_g && A.g.z) ? 2 : 1, zn = (!K.m_on_g && A.g.z) ? 2 : 1;   // G is read twice (dy and z)
     bool ok = false;
-    for (int lines = 128; lines >= 32 && !ok; lines /= 2) {
-      if (HW % lines != 0) continue;
-      if (M / lines < 2 * kNumSMs) continue;                        // too few tiles to stream: slab engine
-      const int a_slot = chunks_a * lines * 128, g_slot = chunks_g * lines * 128;
-      const int zslot = A.g.z ? lines * K.CWg * 16 : 0;
-      for (int pf = 3; pf >= 1 && !ok; --pf) {
-        const int ring = pf + 2;
-        if (fixed + ring * (a_slot + g_slot) + (pf + 1) * zslot <= budget) {
-          K.lines = lines; K.a_lines = lines; K.a_stride = lines * 128; K.g_stride = lines * 128;
-          K.a_slot = a_slot; K.g_slot = g_slot; K.zslot = zslot; K.pf = pf; K.ringA = ring; K.ringG = ring;
-          ok = true;
+    double best = 0.0;
+    for (int ms = 1; ms <= 16; ++ms) {
+      const int mcta = sw_up((cm + ms - 1) / ms, 128);
+      if ((cm + mcta - 1) / mcta != ms) continue;
+      const int n_mt = mcta / 128;
+      if (n_mt > 4) continue;
+      for (int ns = 1; ns <= 8; ++ns) {
+        const int ncta = sw_up((cn + ns - 1) / ns, 8);
+        if ((cn + ncta - 1) / ncta != ns) continue;
+        const int npad = sw_up(ncta, 16);
+        if (npad > 256 || n_mt * npad > 512 || ms * ns > kNumSMs) continue;
+        if (A.dbias && (K.m_on_g ? mcta : ncta) > 256) continue;
+        const int cw_m = (mcta < cm ? mcta : sw_up(cm, 8)) / 8, cw_n = ncta / 8;
+        if (cw_m > SW_PROD_THREADS || cw_n > SW_PROD_THREADS) continue;
+        const int chunks_m = 2 * n_mt, chunks_n = (npad + 63) / 64;
+        const int cwg = K.m_on_g ? cw_m : cw_n;
+        const int kslabs = kNumSMs / (ms * ns);
+        for (int lines = 128; lines >= 32; lines /= 2) {
+          if (HW % lines != 0 || M / lines < 2 * kslabs) continue;
+          const int slot = (chunks_m + chunks_n) * lines * 128;
+          const int zslot = A.g.z ? lines * cwg * 16 : 0;
+          int pf = 0;
+          for (int q = 3; q >= 1 && !pf; --q)
+            if (fixed + (q + 2) * slot + (q + 1) * zslot <= budget) pf = q;
+          if (!pf) continue;
+          // bytes per CTA (relative) + a penalty for short slots (per-slot overhead)
+          const int mw = mcta < cm ? mcta : cm, nw = ncta < cn ? ncta : cn;   // widest slice actually streamed
+          const double cost = (double)(mw * zm + nw * zn) / kslabs * (1.0 + 16.0 / lines);
+          if (!ok || cost < best) {
+            ok = true; best = cost;
+            K.nsplit = ms * ns; K.n_mtiles = n_mt; K.Npad = npad; K.nacc = n_mt;
+            K.asplit = K.m_on_g ? ns : ms;
+            K.nt = K.m_on_g ? ncta : mcta; K.g_w = K.m_on_g ? mcta : ncta;
+            K.CWa = K.m_on_g ? cw_n : cw_m; K.CWg = K.m_on_g ? cw_m : cw_n;
+            K.lines = lines; K.a_lines = lines; K.a_stride = lines * 128; K.g_stride = lines * 128;
+            K.a_slot = (K.m_on_g ? chunks_n : chunks_m) * lines * 128;
+            K.g_slot = (K.m_on_g ? chunks_m : chunks_n) * lines * 128;
+            K.zslot = zslot; K.pf = pf; K.ringA = pf + 2; K.ringG = pf + 2;
+          }
+          break;   // the largest feasible slot for this (ms, ns)
         }
       }
     }
@@ -532,6 +564,7 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     K.g_lbo = 0;
     K.RU = 1; K.HS = 1; K.WS = 1;
     K.units = (int)(M / K.lines);
+    ctas = kNumSMs / K.nsplit;
   }
   K.tmem_cols = 32;
   while (K.tmem_cols < K.nacc * K.Npad) K.tmem_cols *= 2;

@@ -140,7 +140,9 @@ def test_stream_wgrad3x3(lib, cin, cbuf, cout, n, h, w):
 
 @pytest.mark.parametrize("cin,cout,n,h,w,gated", [(24, 144, 2, 144, 144, False), (144, 40, 2, 144, 144, True),
                                                   (240, 64, 3, 128, 112, True), (64, 384, 2, 160, 128, False),
-                                                  (384, 128, 2, 144, 144, True), (48, 24, 2, 144, 144, True)])
+                                                  (384, 128, 2, 144, 144, True), (48, 24, 2, 144, 144, True),
+                                                  (1056, 176, 8, 32, 32, True), (304, 1824, 16, 16, 16, False),
+                                                  (3072, 512, 16, 16, 16, True), (128, 768, 8, 32, 32, False)])
 def test_stream_wgrad1x1(lib, cin, cout, n, h, w, gated):
     rows = n * h * w
     x = mk((rows, cin), 141).to(BF)
