@@ -278,9 +278,8 @@ def breakdown_table(agg: dict) -> list:
 # kernel-class label -> CUDA kernel behind it (for the ncu cross-reference in profiles/)
 KERNEL_OF = {"conv1x1_wgrad": "wgrad_tc_kernel<1,4,4>", "conv3x3_wgrad": "wgrad_tc_kernel<9,2,1>",
              "convT_wgrad": "wgrad_tc_kernel<1,4,4>", "conv3x3": "conv_tc_kernel", "conv3x3_dgrad": "conv_tc_kernel",
-             "conv1x1": "conv_tc_kernel", "conv1x1_dgrad": "conv_tc_kernel", "dwconv_fwd": "dwconv_kernel<MODE=0>",
-             "dwconv_bwd_data": "dwconv_kernel<MODE=1> / dwconv_bwd_data_s2_kernel",
-             "dwconv_bwd_weight": "dwconv_bwd_weight_kernel"}
+             "conv1x1": "conv_tc_kernel", "conv1x1_dgrad": "conv_tc_kernel", "dwconv_fwd": "dw2::dw2_fwd_kernel",
+             "dwconv_bwd": "dw2::dw2_bwd_kernel (fused data + weight gradient)"}
 
 
 def roofline_of(label: str, ws, events_f: list, events_b: list, steps: int, pk: dict, pk_kind: str, step_ms: float) -> dict:

@@ -158,6 +158,15 @@ int32_t s2lc_dwconv_bwd_data(const s2lc_lazygrad* g, const float* w, const s2lc_
                              int32_t C, int32_t k, int32_t s, int32_t dtype, void* stream);
 int32_t s2lc_dwconv_bwd_weight(const s2lc_lazygrad* g, const s2lc_lazy* in, float* dw, int32_t N, int32_t H, int32_t W,
                                int32_t C, int32_t k, int32_t s, int32_t dtype, void* stream);
+/* Fused streaming backward (autograd of efficientnet_unet.py:329-337 in one pass): tiled over INPUT pixels,
+ * writes d(in) = dwconv^T(g) (* act'(in) when apply_act_bwd) (+ residual), the BNBWD statistics of d(in) against
+ * in.raw, and accumulates dW[c,ky,kx] += act(in) * g — g, in.raw and d(in) each cross HBM once.               */
+int32_t s2lc_dwconv_bwd(const s2lc_lazygrad* g, const float* w, const s2lc_lazy* in, int32_t apply_act_bwd,
+                        const void* res, int64_t ld_res, void* out, int64_t ld_out, double* stats, float* dw,
+                        int32_t N, int32_t H, int32_t W, int32_t C, int32_t k, int32_t s, int32_t dtype, void* stream);
+/* Tile-engine forward (one smem tile per CTA, no row ring); kept to cross-check the streaming kernel. */
+int32_t s2lc_dwconv_fwd_tile(const s2lc_lazy* in, const float* w, void* out, double* stats, int32_t N, int32_t H,
+                             int32_t W, int32_t C, int32_t k, int32_t s, int32_t dtype, void* stream);
 
 /* ---- squeeze-excite (efficientnet_unet.py:346-362, :381) ------------------------------------- */
 int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, int32_t C, int32_t dtype, void* stream);

@@ -617,19 +617,17 @@ class Workspace:
             self.meta(self.bwd_meta, 3 * rec.rows_out * sp.c_exp * self.es, desc=bd)
             self.bn_backward(rec.bn2, rec.kbn2)
             g2 = self.lazygrad(da_buf, sp.c_exp, rec.z2, sp.c_exp, rec.bn2)
-            self.B("s2lc_dwconv_bwd_weight", C.byref(g2), C.byref(rec.dw_in), self.gptr(rec.kdw + ".weight"), N, hi, wi,
-                   sp.c_exp, sp.kernel, sp.stride, self.dt)
-            self.meta(self.bwd_meta, (2 * rec.rows_out + rec.rows_in) * sp.c_exp * self.es,
-                      2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
+            gdw = self.gptr(rec.kdw + ".weight")
+            dw_bytes = (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es
+            dw_flops = 4.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2      # data gradient + weight gradient
             prev_rec = blocks[i - 1] if i > 0 else None
             if prev_rec is not None:
                 psk_ptr, psk_ld = skip_grad(prev_rec)
             if sp.expand:
-                self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), None, 0,
-                       dy1_buf.data_ptr(), sp.c_exp, ("SB", rec.bn1.st_b), N, hi, wi, sp.c_exp, sp.kernel, sp.stride,
-                       self.dt)
-                self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
-                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
+                self.B("s2lc_dwconv_bwd", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), 1, None, 0,
+                       dy1_buf.data_ptr(), sp.c_exp, ("SB", rec.bn1.st_b), gdw, N, hi, wi, sp.c_exp, sp.kernel,
+                       sp.stride, self.dt)
+                self.meta(self.bwd_meta, dw_bytes, dw_flops, desc=bd)
                 self.bn_backward(rec.bn1, rec.kbn1)
                 g1 = self.lazygrad(dy1_buf, sp.c_exp, rec.z1, sp.c_exp, rec.bn1)
                 self.wgrad(L.CONV_1X1, rec.x_lazy, g1, N, hi, wi, sp.c_in, sp.c_exp, self.gptr(rec.k1 + ".weight"))
@@ -643,11 +641,11 @@ class Workspace:
             elif prev_rec is not None:
                 # input is the materialised output of block i-1
                 dYp = dY[(i - 1) % 2]
-                self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), None,
-                       dYi.data_ptr() if sp.residual else None, sp.c_out, dYp.data_ptr(), sp.c_in, None, N, hi, wi,
+                self.B("s2lc_dwconv_bwd", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), 0,
+                       dYi.data_ptr() if sp.residual else None, sp.c_out, dYp.data_ptr(), sp.c_in, None, gdw, N, hi, wi,
                        sp.c_exp, sp.kernel, sp.stride, self.dt)
-                self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
-                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
+                self.meta(self.bwd_meta, dw_bytes + (rec.rows_in * sp.c_exp * self.es if sp.residual else 0), dw_flops,
+                          desc=bd)
                 if psk_ptr is not None:
                     self.B("s2lc_add_slice", dYp.data_ptr(), sp.c_in, psk_ptr, psk_ld, dYp.data_ptr(), sp.c_in,
                            rec.rows_in, sp.c_in, self.dt)
@@ -657,10 +655,9 @@ class Workspace:
             else:
                 # block 0: input is the lazy stem output -> gradient w.r.t. the stem BatchNorm output
                 dy0 = dy1_buf
-                self.B("s2lc_dwconv_bwd_data", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), None, 0,
-                       dy0.data_ptr(), c0, ("SB", bn0.st_b), N, hi, wi, sp.c_exp, sp.kernel, sp.stride, self.dt)
-                self.meta(self.bwd_meta, (2 * rec.rows_out + 2 * rec.rows_in) * sp.c_exp * self.es,
-                          2.0 * rec.rows_out * sp.c_exp * sp.kernel ** 2, desc=bd)
+                self.B("s2lc_dwconv_bwd", C.byref(g2), rec.dw_w.data_ptr(), C.byref(rec.dw_in), 1, None, 0,
+                       dy0.data_ptr(), c0, ("SB", bn0.st_b), gdw, N, hi, wi, sp.c_exp, sp.kernel, sp.stride, self.dt)
+                self.meta(self.bwd_meta, dw_bytes, dw_flops, desc=bd)
                 self.bn_backward(bn0, "encoder.stem.1")
                 g0 = self.lazygrad(dy0, c0, z0, c0, bn0)
                 self.B("s2lc_stem_conv_wgrad", self.x_ptr, C.byref(g0), self.gptr("encoder.stem.0.weight"), N,

@@ -510,7 +510,7 @@ using namespace s2lc;
 
 extern "C" {
 
-int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* stats, int32_t N, int32_t H, int32_t W,
+int32_t s2lc_dwconv_fwd_tile(const s2lc_lazy* in, const float* w, void* out, double* stats, int32_t N, int32_t H, int32_t W,
                         int32_t C, int32_t k, int32_t s, int32_t dtype, void* stream) {
   DW_REQ(C, in->ld % 8 == 0)
   cudaStream_t st = (cudaStream_t)stream;

@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
           if (actA && k < WG_BK) {
             float sc[8], sh[8], gt8[8];
             if (a_aff) { wg_ld8(P.a.scale + ach, sc); wg_ld8(P.a.shift + ach, sh); }
-            if (a_gate) wg_ld8(P.a.gate + (int64_t)n * P.Cin + ach, gt8);
+            if (a_gate && px0 + k < mei) wg_ld8(P.a.gate + (int64_t)n * P.Cin + ach, gt8);   // tail pixels: n >= N
 #pragma unroll
             for (int t = 0; t < TAPS; ++t) {
               if (((okA >> (t * MAXPA + p)) & 1u) && a_xf) {

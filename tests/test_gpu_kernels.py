@@ -112,6 +112,56 @@ def test_dwconv_fwd_bwd(lib, prec, k, s, h, w, c):
     dw = torch.zeros(c, 1, k, k, device="cuda")
     L().check(lib.s2lc_dwconv_bwd_weight(C.byref(lg), C.byref(lz), dw.data_ptr(), n, h, w, c, k, s, dt, stream()))
     assert rel_err(dw, gw) < tol * 2
+    # fused streaming backward (one pass: dx + BNBWD statistics + dW) must agree with the same references
+    dx2 = torch.empty(n * h * w, c, dtype=dtype, device="cuda")
+    st3 = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    dw2 = torch.zeros(c, 1, k, k, device="cuda")
+    L().check(lib.s2lc_dwconv_bwd(C.byref(lg), wt.data_ptr(), C.byref(lz), 1, None, 0, dx2.data_ptr(), c,
+                                  st3.data_ptr(), dw2.data_ptr(), n, h, w, c, k, s, dt, stream()))
+    gotx2 = nchw(dx2, n, h, w)
+    assert rel_err(gotx2, gx_bnout) < tol * 2
+    assert rel_err(st3[:c], gotx2.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(st3[c:], (gotx2.double() * nchw(xr, n, h, w).double()).sum((0, 2, 3))) < 1e-5
+    assert rel_err(dw2, gw) < tol * 2
+    # tile-engine forward (kept for cross-checking) against the streaming forward
+    out_t = torch.empty_like(out)
+    L().check(lib.s2lc_dwconv_fwd_tile(C.byref(lz), wt.data_ptr(), out_t.data_ptr(), None, n, h, w, c, k, s, dt,
+                                       stream()))
+    assert rel_err(out_t.float(), out.float()) < tol
+
+
+@pytest.mark.parametrize("k,s,h,w,c", [(3, 1, 64, 96, 24), (5, 1, 32, 32, 176), (5, 2, 64, 64, 240), (3, 2, 128, 64, 144),
+                                       (5, 1, 16, 16, 304), (3, 1, 40, 24, 200)])
+def test_dwconv_stream_plain_residual(lib, k, s, h, w, c):
+    """Streaming dwconv on strip-spanning shapes: identity input (no BN/act, as in the expand-less blocks), residual
+    added to dx, gradient without a BatchNorm behind it but with a per-sample rowscale; bf16 storage."""
+    dtype, dt, tol = DT["bf16"]
+    n = 3
+    xr = nhwc(mk((n, c, h, w), 11), dtype)
+    xq = nchw(xr, n, h, w).requires_grad_(True)
+    wq = mk((c, 1, k, k), 12, 0.3).requires_grad_(True)
+    ref = F.conv2d(same_pad(xq, k, s), wq, stride=s, groups=c)
+    ho, wo = ref.shape[-2:]
+    out = torch.empty(n * ho * wo, c, dtype=dtype, device="cuda")
+    stats = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    lz = lazy(xr, c)
+    L().check(lib.s2lc_dwconv_fwd(C.byref(lz), wq.data_ptr(), out.data_ptr(), stats.data_ptr(), n, h, w, c, k, s, dt,
+                                  stream()))
+    got = nchw(out, n, ho, wo)
+    assert rel_err(got, ref) < tol
+    assert rel_err(stats[:c], got.double().sum((0, 2, 3))) < 1e-5
+    dyr = nhwc(mk((n, c, ho, wo), 13), dtype)
+    rs = torch.tensor([0.5, 1.25, 2.0], device="cuda")
+    g_ref = nchw(dyr, n, ho, wo) * rs.view(-1, 1, 1, 1)
+    gx, gw = torch.autograd.grad(ref, (xq, wq), g_ref)
+    resr = nhwc(mk((n, c, h, w), 14), dtype)
+    lg = lazygrad(dyr, c, rs=rs)
+    dx = torch.empty(n * h * w, c, dtype=dtype, device="cuda")
+    dw = torch.zeros(c, 1, k, k, device="cuda")
+    L().check(lib.s2lc_dwconv_bwd(C.byref(lg), wq.data_ptr(), C.byref(lz), 0, resr.data_ptr(), c, dx.data_ptr(), c,
+                                  None, dw.data_ptr(), n, h, w, c, k, s, dt, stream()))
+    assert rel_err(nchw(dx, n, h, w), gx + nchw(resr, n, h, w)) < tol * 2
+    assert rel_err(dw, gw) < tol * 2
 
 
 # ----------------------------------------------------------------------------------------------- implicit GEMM

@@ -26,7 +26,7 @@ from s2lc_b200._engine import PackedWeight  # noqa: E402
 
 def main() -> None:
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["wgrad3x3", "wgrad1x1", "wgradT", "conv3x3", "conv1x1", "dwfwd", "dwbwd", "dwwgrad"])
+    ap.add_argument("what", choices=["wgrad3x3", "wgrad1x1", "wgradT", "conv3x3", "conv1x1", "dwfwd", "dwbwd", "dwwgrad", "dwbwdf"])
     ap.add_argument("--n", type=int, default=32)
     ap.add_argument("--h", type=int, default=512)
     ap.add_argument("--w", type=int, default=512)
@@ -142,6 +142,18 @@ def main() -> None:
             def run():
                 L.check(lib.s2lc_dwconv_bwd_data(C.byref(lg), wt.data_ptr(), C.byref(la), None, 0, out.data_ptr(), c,
                                                  stats.data_ptr(), n, h, w, c, k, s, L.BF16, st))
+        elif a.what == "dwbwdf":
+            dy, z = rnd(rows_o, c), rnd(rows_o, c)
+            lg = lazygrad(dy, c, c, z)
+            out = torch.empty(rows, c, dtype=bf, device=dev)
+            stats = torch.zeros(2 * c, dtype=torch.float64, device=dev)
+            dw = torch.zeros(c * k * k, dtype=torch.float32, device=dev)
+            nbytes = (2 * rows_o + 2 * rows) * c * 2
+            flops *= 2
+
+            def run():
+                L.check(lib.s2lc_dwconv_bwd(C.byref(lg), wt.data_ptr(), C.byref(la), 1, None, 0, out.data_ptr(), c,
+                                            stats.data_ptr(), dw.data_ptr(), n, h, w, c, k, s, L.BF16, st))
         else:
             dy, z = rnd(rows_o, c), rnd(rows_o, c)
             lg = lazygrad(dy, c, c, z)
