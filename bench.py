@@ -303,8 +303,10 @@ def roofline_of(label: str, ws, events_f: list, events_b: list, steps: int, pk: 
     if os.path.exists(prof):
         with open(prof) as f:
             t = json.load(f)
-        if t.get("kernel_class") == label:
-            traffic = t.get("dram_bytes_per_launch")
+        if t.get("kernel_class") == label:      # ncu capture of ONE launch of this class: scale its DRAM/algorithmic
+            traffic = t.get("dram_bytes_per_launch")   # ratio to the class-average launch the roofline is quoted on
+            if traffic is None and t.get("dram_over_algorithmic"):
+                traffic = t["dram_over_algorithmic"] * nbytes / max(n, 1)
     roof.update({"kernel": label, "cuda_kernel": KERNEL_OF.get(label, label), "launches_per_step": n // max(steps, 1),
                  "avg_launch_ms": ms / max(n, 1), "algorithmic_bytes_per_launch": nbytes / max(n, 1),
                  "algorithmic_flops_per_launch": flops / max(n, 1), "share_of_step": ms / max(steps, 1) / step_ms,

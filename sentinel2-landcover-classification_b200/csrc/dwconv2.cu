@@ -83,6 +83,19 @@ template <> __device__ __forceinline__ void st_pair<float>(float* p, float a, fl
   *reinterpret_cast<float2*>(p) = make_float2(a, b);
 }
 
+// store a channel pair and return it as it will be read back from storage
+template <typename T> __device__ __forceinline__ float2 st_pair_rt(T* p, float2 v);
+template <> __device__ __forceinline__ float2 st_pair_rt<bf16>(bf16* p, float2 v) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+  *reinterpret_cast<__nv_bfloat162*>(p) = h;
+  uint32_t u = *reinterpret_cast<uint32_t*>(&h);
+  return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+}
+template <> __device__ __forceinline__ float2 st_pair_rt<float>(float* p, float2 v) {
+  *reinterpret_cast<float2*>(p) = v;
+  return v;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Ring loader.  issue(): rows [rel0, rel0+nrows) of a WW-pixel x 64-channel window of the source tensor(s) are
 // fetched with cp.async (16 B, L1-bypassing) into a raw STAGE in shared memory where every thread owns private
@@ -118,91 +131,201 @@ template <> struct Raw8<float> {
   }
 };
 
-template <typename T, int NSRC, int WW, int MAXROWS, int NRING, bool FAST>
+__device__ __forceinline__ float2 fmul2(const float2& a, const float2& b) {
+  float2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;"
+      : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 ffma2r(const float2& a, const float2& b, const float2& c) {  // a*b + c
+  float2 d = c;
+  ffma2(d, a, b);
+  return d;
+}
+
+// Thread <-> vector mapping of a pass (NEW rows x WW pixels x 8 vectors of 8 channels):
+//  * WIDE (WW >= 32): thread (px = tid/8, v8 = tid%8) owns the same pixel column in every row (slot j = row j, no
+//    divisions, one bounds check per item) and the WW-32 halo columns go to ONE extra slot of the low threads;
+//  * narrow windows: generic q = tid + j*256 -> (row, px) by constant division.
+template <typename T, int NSRC, int WW, int NEW, int NRING, bool FAST>
 struct Loader {
-  static constexpr int NV = MAXROWS * WW * 8;
-  static constexpr int NVT = (NV + NT - 1) / NT;
-  static constexpr int VB = 8 * sizeof(T);                          // bytes per 8-channel vector
+  static constexpr bool WIDE = WW >= 32;
+  static constexpr int XC = WIDE ? WW - 32 : 0;              // halo columns beyond the 32 main ones
+  static constexpr int NX = NEW * XC * 8;                    // their vectors per pass
+  static constexpr int NXT = NX > 0 ? 1 : 0;
+  static_assert(NX <= NT, "halo columns of a pass must fit one slot");
+  static constexpr int NVT = WIDE ? NEW + NXT : (NEW * WW * 8 + NT - 1) / NT;
+  static constexpr int VB = 8 * sizeof(T);                   // bytes per 8-channel vector
   static constexpr int STAGE_BYTES = NVT * NSRC * NT * VB;
+
+  // per-item state
+  const T* pm[2];       // main column: pointer to (n, row 0, gx, c8) of each source
+  const T* pe[2];       // halo column of this thread
+  int64_t rstride[2];   // elements per source row
+  int gy0, Hs;
+  bool okm, oke;
+  int erow, epx;        // halo slot: row inside the pass, pixel column
+  // generic path
+  int gx0, Ws, n, cb0, C;
+  int64_t ld[2];
+  const T* base[2];
+
+  __device__ __forceinline__ void begin_item(const T* s0, int64_t ld0, const T* s1, int64_t ld1, int n_, int Hs_,
+                                             int Ws_, int gy0_, int gx0_, int cb0_, int C_) {
+    gy0 = gy0_; Hs = Hs_;
+    const int c8 = cb0_ + (threadIdx.x & 7) * 8;
+    if (WIDE) {
+      const int px = threadIdx.x >> 3;
+      const int gx = gx0_ + px;
+      okm = gx >= 0 && gx < Ws_ && c8 < C_;
+      const int64_t img = (int64_t)n_ * Hs_ * Ws_;
+      pm[0] = s0 + (img + gx) * ld0 + c8;
+      pm[1] = s1 + (img + gx) * ld1 + c8;
+      rstride[0] = (int64_t)Ws_ * ld0;
+      rstride[1] = (int64_t)Ws_ * ld1;
+      if (NXT) {
+        erow = threadIdx.x / (XC * 8 > 0 ? XC * 8 : 1);
+        epx = 32 + ((threadIdx.x - erow * (XC * 8)) >> 3);
+        const int gxe = gx0_ + epx;
+        oke = (int)threadIdx.x < NX && gxe >= 0 && gxe < Ws_ && c8 < C_;
+        pe[0] = s0 + (img + gxe) * ld0 + c8;
+        pe[1] = s1 + (img + gxe) * ld1 + c8;
+      }
+    } else {
+      gx0 = gx0_; Ws = Ws_; n = n_; cb0 = cb0_; C = C_;
+      ld[0] = ld0; ld[1] = ld1; base[0] = s0; base[1] = s1;
+    }
+  }
 
   static __device__ __forceinline__ unsigned char* slot(unsigned char* stage, int j, int s) {
     return stage + ((size_t)(j * NSRC + s) * NT + threadIdx.x) * VB;
   }
+  static __device__ __forceinline__ void fetch(unsigned char* stage, int j, const T* a, const T* b) {
+    cp_async16(slot(stage, j, 0), a);
+    if (sizeof(T) == 4) cp_async16(slot(stage, j, 0) + 16, a + 4);
+    if (NSRC == 2) {
+      cp_async16(slot(stage, j, NSRC - 1), b);
+      if (sizeof(T) == 4) cp_async16(slot(stage, j, NSRC - 1) + 16, b + 4);
+    }
+  }
 
-  static __device__ __forceinline__ void issue(unsigned char* stage, const T* s0, int64_t ld0, const T* s1,
-                                               int64_t ld1, int n, int Hs, int Ws, int gy0, int gx0, int rel0,
-                                               int nrows, int cb0, int C) {
-    const int v8 = threadIdx.x & 7;
-    const int c8 = cb0 + v8 * 8;
+  __device__ __forceinline__ void issue(unsigned char* stage, int rel0, int nrows) const {
+    if (WIDE) {
 #pragma unroll
-    for (int j = 0; j < NVT; ++j) {
-      int q = threadIdx.x + j * NT;
-      int row = q / (WW * 8);
-      int px = (q - row * (WW * 8)) >> 3;
-      int gy = gy0 + rel0 + row, gx = gx0 + px;
-      bool v = row < nrows && gy >= 0 && gy < Hs && gx >= 0 && gx < Ws && c8 < C;
-      if (v) {
-        int64_t r = ((int64_t)n * Hs + gy) * Ws + gx;
-        const T* a = s0 + r * ld0 + c8;
-        cp_async16(slot(stage, j, 0), a);
-        if (sizeof(T) == 4) cp_async16(slot(stage, j, 0) + 16, a + 4);
-        if (NSRC == 2) {
-          const T* b = s1 + r * ld1 + c8;
-          cp_async16(slot(stage, j, NSRC - 1), b);
-          if (sizeof(T) == 4) cp_async16(slot(stage, j, NSRC - 1) + 16, b + 4);
+      for (int j = 0; j < NEW; ++j) {
+        const int gy = gy0 + rel0 + j;
+        if (j < nrows && okm && gy >= 0 && gy < Hs) fetch(stage, j, pm[0] + gy * rstride[0], pm[1] + gy * rstride[1]);
+      }
+      if (NXT) {
+        const int gy = gy0 + rel0 + erow;
+        if (oke && erow < nrows && gy >= 0 && gy < Hs) fetch(stage, NEW, pe[0] + gy * rstride[0], pe[1] + gy * rstride[1]);
+      }
+    } else {
+      const int c8 = cb0 + (threadIdx.x & 7) * 8;
+#pragma unroll
+      for (int j = 0; j < NVT; ++j) {
+        int q = threadIdx.x + j * NT;
+        int row = q / (WW * 8);
+        int px = (q - row * (WW * 8)) >> 3;
+        int gy = gy0 + rel0 + row, gx = gx0 + px;
+        if (row < nrows && gy >= 0 && gy < Hs && gx >= 0 && gx < Ws && c8 < C) {
+          int64_t r = ((int64_t)n * Hs + gy) * Ws + gx;
+          fetch(stage, j, base[0] + r * ld[0] + c8, base[1] + r * ld[1] + c8);
         }
       }
     }
     cp_async_commit();
   }
 
-  // mode 0: v = act(v*aux0 + aux1);  mode 1: v = aux0 * v * rs + aux1 * z + aux2;  mode 2: v = v * rs
-  static __device__ __forceinline__ void commit(const unsigned char* stage, float* tile, const float* aux, int Hs,
-                                                int Ws, int gy0, int gx0, int rel0, int nrows, int cb0, int C,
-                                                int mode, int act, float rs) {
+  // transform one staged vector (or zeros) and store it to the fp32 ring
+  // mode 0: v = act(v*aux0 + aux1)  [FAST SiLU: aux pre-scaled by 1/2, v = h*tanh(h)+h];
+  // mode 1: v = (aux0*rs) * v + aux1 * z + aux2;  mode 2: v = v * rs
+  static __device__ __forceinline__ void xform_store(const unsigned char* stage, int j, bool ok, float* dst,
+                                                     const float* aux, int mode, int act, float rs) {
     const int v8 = threadIdx.x & 7;
-    const int c8 = cb0 + v8 * 8;
+    float v[8];
+    if (ok) {
+      Raw8<T>::unpack(slot(const_cast<unsigned char*>(stage), j, 0), v);
+      const float4* a0 = reinterpret_cast<const float4*>(aux + v8 * 8);
+      const float4* a1 = reinterpret_cast<const float4*>(aux + CB + v8 * 8);
+      float4 s0 = a0[0], s1 = a0[1], h0 = a1[0], h1 = a1[1];
+      const float2 A[4] = {{s0.x, s0.y}, {s0.z, s0.w}, {s1.x, s1.y}, {s1.z, s1.w}};
+      const float2 B[4] = {{h0.x, h0.y}, {h0.z, h0.w}, {h1.x, h1.y}, {h1.z, h1.w}};
+      if (mode == 0) {
 #pragma unroll
-    for (int j = 0; j < NVT; ++j) {
-      int q = threadIdx.x + j * NT;
-      int row = q / (WW * 8);
-      int px = (q - row * (WW * 8)) >> 3;
-      if (row >= nrows) continue;
-      int gy = gy0 + rel0 + row, gx = gx0 + px;
-      bool ok = gy >= 0 && gy < Hs && gx >= 0 && gx < Ws && c8 < C;
-      float v[8];
-      if (ok) {
-        Raw8<T>::unpack(slot(const_cast<unsigned char*>(stage), j, 0), v);
-        const float4* a0 = reinterpret_cast<const float4*>(aux + v8 * 8);
-        const float4* a1 = reinterpret_cast<const float4*>(aux + CB + v8 * 8);
-        if (mode == 0) {
-          float4 s0 = a0[0], s1 = a0[1], h0 = a1[0], h1 = a1[1];
-          const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-          const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        for (int i = 0; i < 4; ++i) {
+          float2 u = ffma2r(make_float2(v[2 * i], v[2 * i + 1]), A[i], B[i]);
+          if (FAST && act == S2LC_ACT_SILU) {
+            float2 t = make_float2(tanh_fast(u.x), tanh_fast(u.y));
+            u = ffma2r(u, t, u);
+          } else {
+            u.x = act_f<false>(u.x, act);
+            u.y = act_f<false>(u.y, act);
+          }
+          v[2 * i] = u.x; v[2 * i + 1] = u.y;
+        }
+      } else if (mode == 1) {
+        float z[8];
+        Raw8<T>::unpack(slot(const_cast<unsigned char*>(stage), j, NSRC - 1), z);
+        const float4* a2 = reinterpret_cast<const float4*>(aux + 2 * CB + v8 * 8);
+        float4 t0 = a2[0], t1 = a2[1];
+        const float2 Tt[4] = {{t0.x, t0.y}, {t0.z, t0.w}, {t1.x, t1.y}, {t1.z, t1.w}};
+        const float2 rs2 = make_float2(rs, rs);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = act_f<FAST>(fmaf(v[i], sc[i], sh[i]), act);
-        } else if (mode == 1) {
-          float z[8];
-          Raw8<T>::unpack(slot(const_cast<unsigned char*>(stage), j, NSRC - 1), z);
-          const float4* a2 = reinterpret_cast<const float4*>(aux + 2 * CB + v8 * 8);
-          float4 p0 = a0[0], p1 = a0[1], q0 = a1[0], q1 = a1[1], t0 = a2[0], t1 = a2[1];
-          const float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-          const float qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-          const float tt[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = fmaf(pp[i] * rs, v[i], fmaf(qq[i], z[i], tt[i]));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] *= rs;
+        for (int i = 0; i < 4; ++i) {
+          float2 u = ffma2r(B[i], make_float2(z[2 * i], z[2 * i + 1]), Tt[i]);
+          u = ffma2r(fmul2(A[i], rs2), make_float2(v[2 * i], v[2 * i + 1]), u);
+          v[2 * i] = u.x; v[2 * i + 1] = u.y;
         }
       } else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        for (int i = 0; i < 8; ++i) v[i] *= rs;
       }
-      int slot_r = (rel0 + row) % NRING;
-      float4* dst = reinterpret_cast<float4*>(tile + ((int64_t)slot_r * WW + px) * CB + v8 * 8);
-      dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-      dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    }
+    float4* d4 = reinterpret_cast<float4*>(dst + v8 * 8);
+    d4[0] = make_float4(v[0], v[1], v[2], v[3]);
+    d4[1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+
+  // rbase = ring slot of row rel0
+  __device__ __forceinline__ void commit(const unsigned char* stage, float* tile, const float* aux, int rel0, int rbase,
+                                         int nrows, int mode, int act, float rs) const {
+    if (WIDE) {
+      const int px = threadIdx.x >> 3;
+#pragma unroll
+      for (int j = 0; j < NEW; ++j) {
+        if (j >= nrows) break;
+        const int gy = gy0 + rel0 + j;
+        int sr = rbase + j;
+        if (sr >= NRING) sr -= NRING;
+        xform_store(stage, j, okm && gy >= 0 && gy < Hs, tile + ((size_t)sr * WW + px) * CB, aux, mode, act, rs);
+      }
+      if (NXT) {
+        if ((int)threadIdx.x < NX && erow < nrows) {
+          const int gy = gy0 + rel0 + erow;
+          int sr = rbase + erow;
+          if (sr >= NRING) sr -= NRING;
+          xform_store(stage, NEW, oke && gy >= 0 && gy < Hs, tile + ((size_t)sr * WW + epx) * CB, aux, mode, act, rs);
+        }
+      }
+    } else {
+      const int c8 = cb0 + (threadIdx.x & 7) * 8;
+#pragma unroll
+      for (int j = 0; j < NVT; ++j) {
+        int q = threadIdx.x + j * NT;
+        int row = q / (WW * 8);
+        int px = (q - row * (WW * 8)) >> 3;
+        if (row >= nrows) continue;
+        int gy = gy0 + rel0 + row, gx = gx0 + px;
+        bool ok = gy >= 0 && gy < Hs && gx >= 0 && gx < Ws && c8 < C;
+        int sr = rbase + row;
+        if (sr >= NRING) sr -= NRING;
+        xform_store(stage, j, ok, tile + ((size_t)sr * WW + px) * CB, aux, mode, act, rs);
+      }
     }
   }
 };
@@ -266,8 +389,9 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
   const bool cvalid = c < g.C;
   if (threadIdx.x < CB) {
     int cc = cb0 + threadIdx.x;
-    aux[threadIdx.x] = (cc < g.C && in.scale) ? in.scale[cc] : 1.f;
-    aux[CB + threadIdx.x] = (cc < g.C && in.shift) ? in.shift[cc] : 0.f;
+    const float f = (sizeof(T) == 2 && in.act == S2LC_ACT_SILU) ? 0.5f : 1.f;   // h = u/2 for the tanh form of SiLU
+    aux[threadIdx.x] = f * ((cc < g.C && in.scale) ? in.scale[cc] : 1.f);
+    aux[CB + threadIdx.x] = f * ((cc < g.C && in.shift) ? in.shift[cc] : 0.f);
   }
   if (threadIdx.x < 2 * CB) sstat[threadIdx.x] = 0.f;
   float2 wr[K * K];
@@ -276,6 +400,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
     wr[t] = cvalid ? make_float2(w[(int64_t)c * K * K + t], w[(int64_t)(c + 1) * K * K + t]) : make_float2(0.f, 0.f);
   float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
   const T* src = reinterpret_cast<const T*>(in.raw);
+  Ld ld;
   const int items = g.N * g.ychunks * g.xs;
   int iss = 0, com = 0;  // stage cursors (issue / commit), both advance once per pass
   auto next = [](int& x) { int r = x; x = (x + 1 == NSTAGE) ? 0 : x + 1; return r; };
@@ -287,13 +412,10 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
     int yend = min(y0 + g.YC, g.Hd);
     int nsteps = (yend - y0 + RY - 1) / RY;
     const int gy0 = y0 * S - g.pad_t, gx0 = x0 * S - g.pad_l;
-    auto issue = [&](int rel0, int nr) {
-      Ld::issue(stages + (size_t)next(iss) * Ld::STAGE_BYTES, src, in.ld, src, in.ld, n, g.Hs, g.Ws, gy0, gx0, rel0, nr,
-                cb0, g.C);
-    };
-    auto commit = [&](int rel0, int nr) {
-      Ld::commit(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux, g.Hs, g.Ws, gy0, gx0, rel0, nr, cb0, g.C, 0,
-                 in.act, 1.f);
+    ld.begin_item(src, in.ld, src, in.ld, n, g.Hs, g.Ws, gy0, gx0, cb0, g.C);
+    auto issue = [&](int rel0, int nr) { ld.issue(stages + (size_t)next(iss) * Ld::STAGE_BYTES, rel0, nr); };
+    auto commit = [&](int rel0, int rb, int nr) {
+      ld.commit(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux, rel0, rb, nr, 0, in.act, 1.f);
     };
     // prologue: the PRO leading rows, then steps 0 .. D-1 in flight
 #pragma unroll
@@ -306,8 +428,9 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
     cp_async_wait<D - 1>();
     __syncthreads();  // previous item's readers are done with the ring; aux/sstat initialised
 #pragma unroll
-    for (int pp = 0; pp < PRO_PASSES; ++pp) commit(pp * NEW, min(NEW, PRO - pp * NEW));
-    commit(PRO, NEW);
+    for (int pp = 0; pp < PRO_PASSES; ++pp) commit(pp * NEW, (pp * NEW) % NRING, min(NEW, PRO - pp * NEW));
+    commit(PRO, PRO % NRING, NEW);
+    int cslot = (PRO + NEW) % NRING;  // ring slot the next pass is committed to
     __syncthreads();
     int base = 0;  // ring slot of the first window row of this step
     for (int t = 0; t < nsteps; ++t) {
@@ -338,19 +461,19 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
         }
       }
       if (cvalid) {
+        const int ox0 = x0 + warp * R;
+        const float2 one2 = make_float2(1.f, 1.f);
 #pragma unroll
         for (int dy = 0; dy < RY; ++dy) {
           int oy = y0 + t * RY + dy;
           if (oy >= yend) break;
+          T* op = out + (((int64_t)n * g.Hd + oy) * g.Wd + ox0) * g.C + c;
 #pragma unroll
           for (int r = 0; r < R; ++r) {
-            int ox = x0 + warp * R + r;
-            if (ox >= g.Wd) break;
-            int64_t orow = ((int64_t)n * g.Hd + oy) * g.Wd + ox;
-            float a = roundf_as<T>(acc[dy][r].x), b = roundf_as<T>(acc[dy][r].y);
-            st_pair<T>(out + orow * g.C + c, a, b);
-            s0.x += a; s0.y += b;
-            s1.x = fmaf(a, a, s1.x); s1.y = fmaf(b, b, s1.y);
+            if (ox0 + r >= g.Wd) break;
+            float2 ab = st_pair_rt<T>(op + (int64_t)r * g.C, acc[dy][r]);   // stored (rounded) values
+            ffma2(s0, ab, one2);
+            ffma2(s1, ab, ab);
           }
         }
       }
@@ -359,7 +482,9 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
       if (t + 1 < nsteps) {
         cp_async_wait<D - 1>();   // pass of step t+1 has landed in this thread's slots
         __syncthreads();          // all warps finished reading the rows that are about to be replaced
-        commit(PRO + (t + 1) * NEW, NEW);
+        commit(PRO + (t + 1) * NEW, cslot, NEW);
+        cslot += NEW;
+        if (cslot >= NRING) cslot -= NRING;
         __syncthreads();
       }
     }
@@ -442,6 +567,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
   const T* sdy = reinterpret_cast<const T*>(gin.dy);
   const T* sz = reinterpret_cast<const T*>(gin.z ? gin.z : gin.dy);
   const T* zin = reinterpret_cast<const T*>(in.raw);
+  Ld ld;
   const int items = g.N * g.ychunks * g.xs;
   int iss = 0, com = 0;  // stage cursors (issue / commit), both advance once per pass
   auto next = [](int& x) { int r = x; x = (x + 1 == NSTAGE) ? 0 : x + 1; return r; };
@@ -454,13 +580,10 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
     int nsteps = (yend - y0 + RY - 1) / RY;
     const int gy0 = y0 / S + FL, gx0 = x0 / S + FL;
     const float rs = gin.rowscale ? gin.rowscale[n] : 1.f;
-    auto issue = [&](int rel0, int nr) {
-      Ld::issue(stages + (size_t)next(iss) * Ld::STAGE_BYTES, sdy, gin.ld_dy, sz, gin.ld_z, n, g.Hs, g.Ws, gy0, gx0,
-                rel0, nr, cb0, g.C);
-    };
-    auto commit = [&](int rel0, int nr) {
-      Ld::commit(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux, g.Hs, g.Ws, gy0, gx0, rel0, nr, cb0, g.C,
-                 gmode, 0, rs);
+    ld.begin_item(sdy, gin.ld_dy, sz, gin.ld_z, n, g.Hs, g.Ws, gy0, gx0, cb0, g.C);
+    auto issue = [&](int rel0, int nr) { ld.issue(stages + (size_t)next(iss) * Ld::STAGE_BYTES, rel0, nr); };
+    auto commit = [&](int rel0, int rb, int nr) {
+      ld.commit(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux, rel0, rb, nr, gmode, 0, rs);
     };
     // destination-side operand (saved raw input of the depthwise conv at this warp's RY x R pixels), prefetched
     // one step ahead in registers
@@ -488,8 +611,9 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
     cp_async_wait<D - 1>();
     __syncthreads();
 #pragma unroll
-    for (int pp = 0; pp < PRO_PASSES; ++pp) commit(pp * NEW, min(NEW, PRO - pp * NEW));
-    commit(PRO, NEW);
+    for (int pp = 0; pp < PRO_PASSES; ++pp) commit(pp * NEW, (pp * NEW) % NRING, min(NEW, PRO - pp * NEW));
+    commit(PRO, PRO % NRING, NEW);
+    int cslot = (PRO + NEW) % NRING;
     __syncthreads();
     int base = 0;
     for (int t = 0; t < nsteps; ++t) {
@@ -509,8 +633,9 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
           int ix = x0 + warp * R + r;
           float2 z = zr[dy][r].get();
           bool v = cvalid && iy < yend && ix < g.Wd;
-          a[dy][r].x = v ? act_f<FAST>(fmaf(z.x, isc.x, ish.x), in.act) : 0.f;
-          a[dy][r].y = v ? act_f<FAST>(fmaf(z.y, isc.y, ish.y), in.act) : 0.f;
+          float2 u = ffma2r(z, isc, ish);
+          a[dy][r].x = v ? act_f<FAST>(u.x, in.act) : 0.f;
+          a[dy][r].y = v ? act_f<FAST>(u.y, in.act) : 0.f;
           acc[dy][r] = make_float2(0.f, 0.f);
         }
       }
@@ -539,31 +664,44 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
         }
       }
       if (cvalid) {
+        const int ix0 = x0 + warp * R;
+        const float2 one2 = make_float2(1.f, 1.f);
+        const bool silu_fast = FAST && in.act == S2LC_ACT_SILU;
 #pragma unroll
         for (int dy = 0; dy < RY; ++dy) {
           int iy = y0 + t * RY + dy;
           if (iy >= yend) break;
+          const int64_t orow0 = ((int64_t)n * g.Hd + iy) * g.Wd + ix0;
+          T* op = out + orow0 * ld_out + c;
+          const T* rp = res ? res + orow0 * ld_res + c : nullptr;
 #pragma unroll
           for (int r = 0; r < R; ++r) {
-            int ix = x0 + warp * R + r;
-            if (ix >= g.Wd) break;
-            int64_t orow = ((int64_t)n * g.Hd + iy) * g.Wd + ix;
+            if (ix0 + r >= g.Wd) break;
             float2 z = zr[dy][r].get();
-            float dxa = acc[dy][r].x, dxb = acc[dy][r].y;
+            float2 dx = acc[dy][r];
             if (apply_act_bwd) {
-              dxa *= act_d<FAST>(fmaf(z.x, isc.x, ish.x), in.act);
-              dxb *= act_d<FAST>(fmaf(z.y, isc.y, ish.y), in.act);
+              float2 u = ffma2r(z, isc, ish);
+              float2 d;
+              if (silu_fast) {  // s = (1 + tanh(u/2))/2;  act' = s * (1 + u*(1-s))
+                const float2 half2 = make_float2(0.5f, 0.5f);
+                float2 hu = fmul2(u, half2);
+                float2 sg = ffma2r(make_float2(tanh_fast(hu.x), tanh_fast(hu.y)), half2, half2);
+                float2 oms = ffma2r(sg, make_float2(-1.f, -1.f), one2);
+                d = fmul2(sg, ffma2r(u, oms, one2));
+              } else {
+                d = make_float2(act_d<false>(u.x, in.act), act_d<false>(u.y, in.act));
+              }
+              dx = fmul2(dx, d);
             }
-            if (res) {
+            if (rp) {
               Pair<T> e;
-              e.load(res + orow * ld_res + c);
+              e.load(rp + (int64_t)r * ld_res);
               float2 ef = e.get();
-              dxa += ef.x; dxb += ef.y;
+              dx.x += ef.x; dx.y += ef.y;
             }
-            dxa = roundf_as<T>(dxa); dxb = roundf_as<T>(dxb);
-            st_pair<T>(out + orow * ld_out + c, dxa, dxb);
-            s0.x += dxa; s0.y += dxb;
-            s1.x = fmaf(dxa, z.x, s1.x); s1.y = fmaf(dxb, z.y, s1.y);
+            float2 st = st_pair_rt<T>(op + (int64_t)r * ld_out, dx);
+            ffma2(s0, st, one2);
+            ffma2(s1, st, z);
           }
         }
       }
@@ -572,7 +710,9 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
       if (t + 1 < nsteps) {
         cp_async_wait<D - 1>();
         __syncthreads();
-        commit(PRO + (t + 1) * NEW, NEW);
+        commit(PRO + (t + 1) * NEW, cslot, NEW);
+        cslot += NEW;
+        if (cslot >= NRING) cslot -= NRING;
         __syncthreads();
       }
     }
