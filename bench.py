@@ -19,6 +19,10 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# NCCL writes its "NCCL version ..." banner to STDOUT at NCCL_DEBUG=VERSION; stdout must carry ONE JSON line
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
