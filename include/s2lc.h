@@ -214,6 +214,14 @@ int32_t s2lc_loss_fwd_bwd(const void* logits, int64_t ld, const int64_t* y, cons
 int32_t s2lc_scale_inplace(void* x, int64_t ld, const float* factor_dev, int64_t rows, int32_t C, int32_t dtype,
                            void* stream);
 
+/* ---- per-step metrics (next row f2) and the uint8 class map of a mosaic writer (next row f4):
+ * train_segmentation.py:145 `update_metrics(predictions=logits.argmax(dim=1), labels=y)` -> torchmetrics confusion
+ * matrix / IoU / accuracy / F1 (:53-67).  One pass: counts[target * C + argmax] += 1 over ALL pixels whose target is in
+ * [0, C) (int64 [C, C], accumulated — the caller zeroes it; ignore_index is applied on the host by dropping that row)
+ * and/or pred[row] = argmax (uint8).  `y`/`counts` or `pred` may be NULL.  First maximum wins, as torch.argmax.     */
+int32_t s2lc_argmax_confusion(const void* logits, int64_t ld, const int64_t* y, int64_t* counts, uint8_t* pred,
+                              int64_t rows, int32_t n_classes, int32_t dtype, void* stream);
+
 /* ---- optimizer (next row f1): torch.optim.Adam with L2 weight decay, train_segmentation.py:110-114 */
 int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                        float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,

@@ -59,9 +59,12 @@ class SegmentationStep:
     """One optimisation step of the reference loop on one device."""
 
     def __init__(self, net: EfficientnetUnet, loss_fn, lr: float = 1.5e-6, weight_decay: float = 0.05,
-                 fused_optimizer: bool = True) -> None:
+                 fused_optimizer: bool = True, metrics=None) -> None:
         self.net, self.loss_fn = net, loss_fn
         self.fused = fused_optimizer
+        # optional ``metrics.SegmentationMetrics``: the reference's ``update_metrics(logits.argmax(1), y)`` (:145),
+        # one extra kernel pass over the logits per step instead of four torchmetrics updates
+        self.metrics = metrics
         if fused_optimizer:
             self.optimizer = FusedAdam(net, lr=lr, weight_decay=weight_decay)
             net.engine().direct_grad = True
@@ -73,6 +76,8 @@ class SegmentationStep:
             self.optimizer.zero_grad(set_to_none=True)
         logits = self.net(x)
         loss = self.loss_fn(logits, y)
+        if self.metrics is not None:
+            self.metrics.update(logits.detach(), y)
         loss.backward()
         return loss.detach()
 
