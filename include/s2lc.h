@@ -222,6 +222,15 @@ int32_t s2lc_scale_inplace(void* x, int64_t ld, const float* factor_dev, int64_t
 int32_t s2lc_argmax_confusion(const void* logits, int64_t ld, const int64_t* y, int64_t* counts, uint8_t* pred,
                               int64_t rows, int32_t n_classes, int32_t dtype, void* stream);
 
+/* ---- input pipeline on the device (next row f3): s2osm_dataset.py:51-71 + s2osm_datamodule.py:75-87 +
+ * cnes_labell_mappings.py:85-95.  raw int16 [N, C, Hs, Ws] tiles and uint8 [N, Hs, Ws] labels -> crop (crop_yx[n] =
+ * top, left; bounds are the caller's contract: 0 <= top <= Hs-crop) -> horizontal / vertical flip (flip_hv[n], may be
+ * NULL) -> x = (raw - mean*mpv) * (1/(std*mpv)) fp32 [N, C, crop, crop]; y = lut[label] (lut: 256 x int64 or NULL =
+ * identity) int64 [N, crop, crop].  x or y may be NULL to skip that half.                                          */
+int32_t s2lc_prepare_batch(const int16_t* raw, const uint8_t* labels, const int32_t* crop_yx, const uint8_t* flip_hv,
+                           const float* mean, const float* stdv, const int64_t* lut, float* x, int64_t* y, int32_t N,
+                           int32_t C, int32_t Hs, int32_t Ws, int32_t crop, float max_pixel_value, void* stream);
+
 /* ---- optimizer (next row f1): torch.optim.Adam with L2 weight decay, train_segmentation.py:110-114 */
 int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                        float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
