@@ -60,7 +60,7 @@ def test_b5_512_fp32_tier_b():
     assert rows[0][0] <= 1e-1, rows[:5]     # vs the fp32 oracle: bounded by mask-flip noise on both sides
 
 
-@pytest.mark.parametrize("version,size,batch", [("b0", 224, 2), ("b5", 224, 2), ("b5", 512, 1)])
+@pytest.mark.parametrize("version,size,batch", [("b0", 224, 2), ("b5", 224, 2), ("b5", 512, 1), ("b7", 1024, 1)])
 def test_bf16_within_tolerance(version, size, batch):
     """bf16 mode against the fp32 oracle, next to the reference's OWN bf16 path (torch.autocast on the GPU, what
     Lightning's precision="bf16" runs) against the same fp32 oracle.  With these random (untrained) weights the
