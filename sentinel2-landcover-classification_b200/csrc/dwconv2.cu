@@ -786,7 +786,8 @@ static int32_t launch_fwd(const s2lc_lazy* in, const float* w, void* out, double
   static int resident = resident_ctas(kern, Cfg::SMEM);
   plan_strips(g, Cfg::TW, RY, cblocks, resident);
   long items = (long)g.N * g.xs * g.ychunks;
-  int gx = (resident + cblocks - 1) / cblocks;
+  int gx = resident / cblocks;   // never more CTAs than are co-resident: a partial second wave doubles the time
+  if (gx < 1) gx = 1;
   if (gx > items) gx = (int)items;
   kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*in, w, (T*)out, stats, g);
   return check_launch("dwconv2_fwd");
@@ -808,7 +809,8 @@ static int32_t launch_bwd(const s2lc_lazygrad* gin, const float* w, const s2lc_l
   static int resident = resident_ctas(kern, Cfg::SMEM);
   plan_strips(g, Cfg::TW, RY, cblocks, resident);
   long items = (long)g.N * g.xs * g.ychunks;
-  int gx = (resident + cblocks - 1) / cblocks;
+  int gx = resident / cblocks;   // never more CTAs than are co-resident: a partial second wave doubles the time
+  if (gx < 1) gx = 1;
   if (gx > items) gx = (int)items;
   kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*gin, w, *in, apply_act_bwd, (const T*)res, ld_res, (T*)out, ld_out,
                                                  stats, dw, g);
