@@ -195,9 +195,38 @@ __global__ void bn_bwd_reduce_kernel(const T* __restrict__ dy, int64_t ld_dy, co
 }
 
 // ------------------------------------------------------------------------------------------ squeeze-excite
+// The streaming squeeze-excite kernels are latency-bound unless several rows are in flight per thread AND enough
+// blocks are resident: rows are fetched as RAW 16 B vectors (4 registers each, converted only when consumed) SE_U at a
+// time, registers are capped at 64 (4 blocks of 256 threads per SM) and the grid never exceeds the resident blocks.
+template <typename T> struct RawV8;
+template <> struct RawV8<bf16> {
+  uint4 u;
+  __device__ __forceinline__ void load(const bf16* p) { u = __ldg(reinterpret_cast<const uint4*>(p)); }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+};
+template <> struct RawV8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) {
+    a = __ldg(reinterpret_cast<const float4*>(p));
+    b = __ldg(reinterpret_cast<const float4*>(p + 4));
+  }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+template <typename T> struct SeU { static constexpr int value = sizeof(T) == 2 ? 4 : 2; };   // rows in flight
+constexpr int SE_BLOCKS_PER_SM = 4;
+constexpr int SE_APPLY_BLOCKS_PER_SM = 3;   // se_bwd_apply holds 4 per-channel vectors + 2 accumulators: 85 registers
 // pooled[n, c] += (1/HW) * sum_{rows of sample n in this split} act(z*scale+shift)
 template <typename T, bool WITH_DA>
-__global__ void se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t ld_da, float* __restrict__ out, int HW,
+__global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t ld_da, float* __restrict__ out, int HW,
                                int C, float mul) {
   // grid: (splits, N).  WITH_DA: out[n,c] += sum da*act(u)  (d gate), else mean of act(u).
   const int CV = C / 8;
@@ -216,17 +245,30 @@ __global__ void se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t l
         sc[j] = in.scale ? in.scale[cv * 8 + j] : 1.f;
         sh[j] = in.shift ? in.shift[cv * 8 + j] : 0.f;
       }
-      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += gridDim.x * it.rows_par) {
-        float v[8];
-        Vec8<T>::load(raw + (int64_t)r * in.ld + cv * 8, v);
-        if (WITH_DA) {
-          float d[8];
-          Vec8<T>::load(dap + (int64_t)r * ld_da + cv * 8, d);
+      constexpr int U = SeU<T>::value;
+      const int stride = gridDim.x * it.rows_par;
+      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += U * stride) {
+        RawV8<T> rv[U], rd[U];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] += d[j] * act_fwd(v[j] * sc[j] + sh[j], in.act);
-        } else {
+        for (int u = 0; u < U; ++u) {
+          const int rr = r + u * stride;
+          if (rr < HW) {
+            rv[u].load(raw + (int64_t)rr * in.ld + cv * 8);
+            if (WITH_DA) rd[u].load(dap + (int64_t)rr * ld_da + cv * 8);
+          }
+        }
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] += act_fwd(v[j] * sc[j] + sh[j], in.act);
+        for (int u = 0; u < U; ++u) {
+          if (r + u * stride < HW) {
+            float v[8], d[8];
+            rv[u].unpack(v);
+            if (WITH_DA) rd[u].unpack(d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float a = act_fwd(fmaf(v[j], sc[j], sh[j]), in.act);
+              acc[j] = WITH_DA ? fmaf(d[j], a, acc[j]) : acc[j] + a;
+            }
+          }
         }
       }
     }
@@ -379,7 +421,7 @@ __global__ void __launch_bounds__(256) se_fc_bwd_weight_kernel(const float* __re
 
 // da <- (da*gate + dpool/HW) * act'(u), BNBWD stats against z
 template <typename T>
-__global__ void se_bwd_apply_kernel(T* __restrict__ da, int64_t ld_da, s2lc_lazy in, const float* __restrict__ dpool,
+__global__ void __launch_bounds__(256, SE_APPLY_BLOCKS_PER_SM) se_bwd_apply_kernel(T* __restrict__ da, int64_t ld_da, s2lc_lazy in, const float* __restrict__ dpool,
                                     double* stats, int HW, int C, float inv_hw) {
   extern __shared__ float smem[];
   const int CV = C / 8;
@@ -400,19 +442,36 @@ __global__ void se_bwd_apply_kernel(T* __restrict__ da, int64_t ld_da, s2lc_lazy
         g[j] = in.gate ? in.gate[(int64_t)n * C + c] : 1.f;
         dp[j] = dpool ? dpool[(int64_t)n * C + c] * inv_hw : 0.f;
       }
-      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += gridDim.x * it.rows_par) {
-        float z[8], d[8];
-        Vec8<T>::load(raw + (int64_t)r * in.ld + cv * 8, z);
-        Vec8<T>::load(dap + (int64_t)r * ld_da + cv * 8, d);
+      constexpr int U = 2;
+      const int stride = gridDim.x * it.rows_par;
+      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += U * stride) {
+        RawV8<T> rz[U], rd[U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float u = z[j] * sc[j] + sh[j];
-          float v = roundf_as<T>((d[j] * g[j] + dp[j]) * act_bwd(u, in.act));
-          d[j] = v;
-          acc[0][j] += v;
-          acc[1][j] += v * z[j];
+        for (int u = 0; u < U; ++u) {
+          const int rr = r + u * stride;
+          if (rr < HW) {
+            rz[u].load(raw + (int64_t)rr * in.ld + cv * 8);
+            rd[u].load(dap + (int64_t)rr * ld_da + cv * 8);
+          }
         }
-        Vec8<T>::store(dap + (int64_t)r * ld_da + cv * 8, d);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int rr = r + u * stride;
+          if (rr < HW) {
+            float z[8], d[8];
+            rz[u].unpack(z);
+            rd[u].unpack(d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float pre = z[j] * sc[j] + sh[j];
+              float v = roundf_as<T>((d[j] * g[j] + dp[j]) * act_bwd(pre, in.act));
+              d[j] = v;
+              acc[0][j] += v;
+              acc[1][j] += v * z[j];
+            }
+            Vec8<T>::store(dap + (int64_t)rr * ld_da + cv * 8, d);
+          }
+        }
       }
     }
     flush_stats<2>(acc, it, cv0, C, stats, smem);
@@ -726,10 +785,10 @@ int32_t s2lc_bn_bwd_reduce(const void* dy, int64_t ld_dy, const void* z, int64_t
   return check_launch("bn_bwd_reduce");
 }
 
-static inline int se_splits(int N, int HW, int C) {
+static inline int se_splits(int N, int HW, int C, int blocks_per_sm = SE_BLOCKS_PER_SM) {
   int cvb = C / 8 < 256 ? C / 8 : 256;
   int rows_par = 256 / cvb;
-  int want = (kNumSMs * 4 + N - 1) / N;
+  int want = (kNumSMs * blocks_per_sm) / N;   // floor: one wave of resident blocks, never a partial second one
   int maxs = (HW + rows_par * 4 - 1) / (rows_par * 4);
   int s = want < maxs ? want : maxs;
   return s < 1 ? 1 : s;
@@ -789,7 +848,7 @@ int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, co
 int32_t s2lc_se_bwd_apply(void* da, int64_t ld_da, const s2lc_lazy* in, const float* dpool, double* stats, int32_t N,
                           int32_t HW, int32_t C, int32_t dtype, void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_da % 8 == 0, S2LC_ERR_ALIGN, "se_bwd_apply: alignment (C=%d)", C);
-  dim3 grid(se_splits(N, HW, C), N);
+  dim3 grid(se_splits(N, HW, C, SE_APPLY_BLOCKS_PER_SM), N);
   DISPATCH_T(dtype, (se_bwd_apply_kernel<T><<<grid, 256, stats_smem(C, 2), (cudaStream_t)stream>>>(
                         (T*)da, ld_da, *in, dpool, stats, HW, C, 1.f / (float)HW)));
   return check_launch("se_bwd_apply");
