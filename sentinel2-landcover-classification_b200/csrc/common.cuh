@@ -83,6 +83,31 @@ __device__ __forceinline__ float act_bwd(float u, int act) {  // d act(u) / du
   return 1.f;
 }
 
+// bf16-storage engines: sigmoid through ONE MUFU (tanh.approx, relative error ~2^-11 — far below the bf16 rounding of
+// the tensors these values are stored to) instead of ex2 + rcp; the fp32 verification engines keep the exact form.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float silu_fast(float u) {
+  const float h = 0.5f * u;
+  return fmaf(h, tanh_approx(h), h);
+}
+__device__ __forceinline__ float act_fwd_fast(float u, int act) {
+  if (act == S2LC_ACT_SILU) return silu_fast(u);
+  if (act == S2LC_ACT_RELU) return fmaxf(u, 0.f);
+  return u;
+}
+__device__ __forceinline__ float act_bwd_fast(float u, int act) {
+  if (act == S2LC_ACT_SILU) {
+    const float s = fmaf(0.5f, tanh_approx(0.5f * u), 0.5f);
+    return s * fmaf(u, 1.f - s, 1.f);
+  }
+  if (act == S2LC_ACT_RELU) return u > 0.f ? 1.f : 0.f;
+  return 1.f;
+}
+
 // ------------------------------------------------------------------ lazy sources, element-wise (generic path)
 // value(row, c) of a forward lazy activation; n = sample index of the row, C = channel count (gate row stride)
 template <typename T>

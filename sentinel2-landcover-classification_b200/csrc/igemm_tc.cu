@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) conv_tc_kernel(ConvArgs P, int 
             }
             if (act != S2LC_ACT_NONE) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j], act);
+              for (int j = 0; j < 8; ++j) v[j] = act_fwd_fast(v[j], act);
             }
             if (has_gate) {
               float g[8];
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) conv_tc_kernel(ConvArgs P, int 
             if (j < nvalid) {
               float u = zp[j];
               if (P.prev.scale) u = fmaf(u, __ldg(P.prev.scale + col0 + j), __ldg(P.prev.shift + col0 + j));
-              acc[j] *= act_bwd(u, P.prev.act);
+              acc[j] *= act_bwd_fast(u, P.prev.act);
             }
         }
       }

@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
                 for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
               } else if (act == S2LC_ACT_SILU) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) v[k] = v[k] * sigmoidf_(v[k]);
+                for (int k = 0; k < 8; ++k) v[k] = silu_fast(v[k]);
               }
               if (gate) {
 #pragma unroll
@@ -510,7 +510,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
         } else if (prev_act == S2LC_ACT_SILU) {
 #pragma unroll
           for (int j = 0; j < 16; ++j)
-            acc[j] *= act_bwd(fmaf(zp[j], evec[256 + lc0 + j], evec[512 + lc0 + j]), S2LC_ACT_SILU);
+            acc[j] *= act_bwd_fast(fmaf(zp[j], evec[256 + lc0 + j], evec[512 + lc0 + j]), S2LC_ACT_SILU);
         }
         // round to the stored precision (statistics must see what the consumer will read back)
         uint4 o0, o1;

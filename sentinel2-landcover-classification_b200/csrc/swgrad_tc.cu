@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
               for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
             } else if (act == S2LC_ACT_SILU) {
 #pragma unroll
-              for (int k = 0; k < 8; ++k) v[k] = v[k] * sigmoidf_(v[k]);
+              for (int k = 0; k < 8; ++k) v[k] = silu_fast(v[k]);
             }
             if (gate) {
 #pragma unroll

@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_tc_kernel(WgradArgs P, Wg
                 }
                 if (a_act != S2LC_ACT_NONE) {
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j], a_act);
+                  for (int j = 0; j < 8; ++j) v[j] = act_fwd_fast(v[j], a_act);
                 }
                 if (a_gate) {
 #pragma unroll
