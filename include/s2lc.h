@@ -231,6 +231,20 @@ int32_t s2lc_prepare_batch(const int16_t* raw, const uint8_t* labels, const int3
                            const float* mean, const float* stdv, const int64_t* lut, float* x, int64_t* y, int32_t N,
                            int32_t C, int32_t Hs, int32_t Ws, int32_t crop, float max_pixel_value, void* stream);
 
+/* ---- mosaic inference writer (next row f4): replaces experiments/inference_demo.py:14-41 (Lightning predict +
+ * torch.save of whole logit tensors, argmax later on the CPU) and train_segmentation.py:106-107 predict_step.
+ * s2lc_gather_tiles: B tiles of tile x tile px cut from ONE int16 scene [C, Hs, Ws] at origin_yx[b] = (top, left)
+ * (may overhang: outside pixels replicate the nearest edge) and normalised as in s2lc_prepare_batch -> x fp32
+ * [B, C, tile, tile].  s2lc_argmax_mosaic: argmax over the class axis of NHWC logits [B, tile, tile, ld >= n_classes]
+ * written as uint8 into mosaic[Hm, ld_mosaic] at origin_yx[b] + (ky, kx) for the tile centre margin <= ky, kx <
+ * tile - margin; pixels landing outside the mosaic are dropped.                                                     */
+int32_t s2lc_gather_tiles(const int16_t* scene, const int32_t* origin_yx, const float* mean, const float* stdv,
+                          float* x, int32_t B, int32_t C, int32_t Hs, int32_t Ws, int32_t tile, float max_pixel_value,
+                          void* stream);
+int32_t s2lc_argmax_mosaic(const void* logits, int64_t ld, const int32_t* origin_yx, uint8_t* mosaic,
+                           int64_t ld_mosaic, int32_t B, int32_t tile, int32_t margin, int32_t Hm, int32_t Wm,
+                           int32_t n_classes, int32_t dtype, void* stream);
+
 /* ---- optimizer (next row f1): torch.optim.Adam with L2 weight decay, train_segmentation.py:110-114 */
 int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                        float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,

@@ -45,6 +45,32 @@ __global__ void __launch_bounds__(256) prepare_batch_kernel(const int16_t* __res
   }
 }
 
+// Mosaic inference (row f4): cut B tiles of t x t pixels out of ONE resident int16 scene [C, Hs, Ws] at arbitrary
+// (possibly negative / overhanging) origins and normalise them.  Pixels outside the scene replicate the nearest edge
+// pixel, so border tiles see plausible context instead of a zero cliff; the mosaic writer never keeps them.
+__global__ void __launch_bounds__(256) gather_tiles_kernel(const int16_t* __restrict__ scene,
+                                                           const int32_t* __restrict__ origin_yx,
+                                                           const float* __restrict__ mean, const float* __restrict__ stdv,
+                                                           float* __restrict__ x, int B, int C, int Hs, int Ws, int t,
+                                                           float max_pixel_value) {
+  const int64_t total = (int64_t)B * t * t;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % t);
+    const int oy = (int)((i / t) % t);
+    const int b = (int)(i / ((int64_t)t * t));
+    int sy = origin_yx[2 * b] + oy, sx = origin_yx[2 * b + 1] + ox;
+    sy = sy < 0 ? 0 : (sy >= Hs ? Hs - 1 : sy);
+    sx = sx < 0 ? 0 : (sx >= Ws ? Ws - 1 : sx);
+    const int64_t sp = (int64_t)sy * Ws + sx;
+    for (int c = 0; c < C; ++c) {
+      const float v = (float)scene[(int64_t)c * Hs * Ws + sp];
+      const float m = mean[c] * max_pixel_value;
+      const float r = 1.0f / (stdv[c] * max_pixel_value);
+      x[(((int64_t)b * C + c) * t + oy) * t + ox] = (v - m) * r;
+    }
+  }
+}
+
 }  // namespace s2lc
 
 using namespace s2lc;
@@ -64,4 +90,19 @@ extern "C" int32_t s2lc_prepare_batch(const int16_t* raw, const uint8_t* labels,
   prepare_batch_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(raw, labels, crop_yx, flip_hv, mean, stdv, lut,
                                                                            x, y, N, C, Hs, Ws, crop, max_pixel_value);
   return check_launch("prepare_batch");
+}
+
+extern "C" int32_t s2lc_gather_tiles(const int16_t* scene, const int32_t* origin_yx, const float* mean,
+                                     const float* stdv, float* x, int32_t B, int32_t C, int32_t Hs, int32_t Ws,
+                                     int32_t tile, float max_pixel_value, void* stream) {
+  S2LC_REQUIRE(scene && origin_yx && mean && stdv && x, S2LC_ERR_SHAPE, "gather_tiles: null pointer");
+  S2LC_REQUIRE(B >= 0 && C > 0 && Hs > 0 && Ws > 0 && tile > 0, S2LC_ERR_SHAPE,
+               "gather_tiles: bad geometry (B=%d C=%d %dx%d tile=%d)", B, C, Hs, Ws, tile);
+  if (B == 0) return S2LC_OK;
+  const int64_t total = (int64_t)B * tile * tile;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
+  gather_tiles_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(scene, origin_yx, mean, stdv, x, B, C, Hs, Ws,
+                                                                          tile, max_pixel_value);
+  return check_launch("gather_tiles");
 }

@@ -63,6 +63,55 @@ static int32_t launch_argmax(const void* logits, int64_t ld, const int64_t* y, i
   return check_launch("argmax_confusion");
 }
 
+// Mosaic writer (row f4): argmax of B tiles of t x t logits written straight into the uint8 scene mosaic.  Only the
+// centre of each tile (margin px trimmed on every side) is kept, and only where it lands inside the mosaic, so tiles
+// predicted with overlapping context tile the scene exactly once.  One thread per kept pixel; 1 B written per pixel.
+template <typename T, int CLS>
+__global__ void __launch_bounds__(256) argmax_mosaic_kernel(const T* __restrict__ logits, int64_t ld,
+                                                            const int32_t* __restrict__ origin_yx,
+                                                            uint8_t* __restrict__ mosaic, int64_t ld_mosaic, int B, int t,
+                                                            int margin, int Hm, int Wm) {
+  const int keep = t - 2 * margin;
+  const int64_t total = (int64_t)B * keep * keep;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int kx = (int)(i % keep) + margin;
+    const int ky = (int)((i / keep) % keep) + margin;
+    const int b = (int)(i / ((int64_t)keep * keep));
+    const int my = origin_yx[2 * b] + ky, mx = origin_yx[2 * b + 1] + kx;
+    if (my < 0 || my >= Hm || mx < 0 || mx >= Wm) continue;
+    const T* row = logits + (((int64_t)b * t + ky) * t + kx) * ld;
+    float best = ldf<T>(row);
+    int arg = 0;
+#pragma unroll
+    for (int c = 1; c < CLS; ++c) {
+      float v = ldf<T>(row + c);
+      if (v > best) { best = v; arg = c; }
+    }
+    mosaic[(int64_t)my * ld_mosaic + mx] = (uint8_t)arg;
+  }
+}
+
+template <typename T>
+static int32_t launch_mosaic(const void* logits, int64_t ld, const int32_t* origin_yx, uint8_t* mosaic, int64_t ldm,
+                             int B, int t, int margin, int Hm, int Wm, int n_classes, cudaStream_t st) {
+  const int keep = t - 2 * margin;
+  int64_t blocks = ((int64_t)B * keep * keep + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
+#define AMM(C_)                                                                                                   \
+  case C_:                                                                                                        \
+    argmax_mosaic_kernel<T, C_><<<(unsigned)blocks, 256, 0, st>>>((const T*)logits, ld, origin_yx, mosaic, ldm, B, t, \
+                                                                  margin, Hm, Wm);                                \
+    break;
+  switch (n_classes) {
+    AMM(2) AMM(3) AMM(4) AMM(5) AMM(6) AMM(7) AMM(8) AMM(9) AMM(10) AMM(11) AMM(12) AMM(13) AMM(14) AMM(15) AMM(16)
+    default:
+      set_error("argmax_mosaic: n_classes=%d unsupported (2..16)", n_classes);
+      return S2LC_ERR_SHAPE;
+  }
+#undef AMM
+  return check_launch("argmax_mosaic");
+}
+
 }  // namespace s2lc
 
 using namespace s2lc;
@@ -79,5 +128,23 @@ extern "C" int32_t s2lc_argmax_confusion(const void* logits, int64_t ld, const i
   if (dtype == S2LC_F32) return launch_argmax<float>(logits, ld, y, counts, pred, rows, n_classes, st);
   if (dtype == S2LC_BF16) return launch_argmax<s2lc::bf16>(logits, ld, y, counts, pred, rows, n_classes, st);
   set_error("argmax_confusion: bad dtype %d", dtype);
+  return S2LC_ERR_SHAPE;
+}
+
+extern "C" int32_t s2lc_argmax_mosaic(const void* logits, int64_t ld, const int32_t* origin_yx, uint8_t* mosaic,
+                                      int64_t ld_mosaic, int32_t B, int32_t tile, int32_t margin, int32_t Hm,
+                                      int32_t Wm, int32_t n_classes, int32_t dtype, void* stream) {
+  S2LC_REQUIRE(logits && origin_yx && mosaic, S2LC_ERR_SHAPE, "argmax_mosaic: null pointer");
+  S2LC_REQUIRE(B >= 0 && tile > 0 && margin >= 0 && 2 * margin < tile && Hm > 0 && Wm > 0 && ld >= n_classes &&
+                   ld_mosaic >= Wm,
+               S2LC_ERR_SHAPE, "argmax_mosaic: bad geometry (B=%d tile=%d margin=%d mosaic %dx%d)", B, tile, margin, Hm,
+               Wm);
+  if (B == 0) return S2LC_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == S2LC_F32)
+    return launch_mosaic<float>(logits, ld, origin_yx, mosaic, ld_mosaic, B, tile, margin, Hm, Wm, n_classes, st);
+  if (dtype == S2LC_BF16)
+    return launch_mosaic<s2lc::bf16>(logits, ld, origin_yx, mosaic, ld_mosaic, B, tile, margin, Hm, Wm, n_classes, st);
+  set_error("argmax_mosaic: bad dtype %d", dtype);
   return S2LC_ERR_SHAPE;
 }

@@ -171,3 +171,52 @@ def test_make_buckets_sizes():
     numels = {f"p{i}": 100 for i in range(10)}
     b = make_buckets(offsets, numels, 1000, 250)
     assert [(x[0], x[1]) for x in b] == [(0, 300), (300, 600), (600, 900), (900, 1000)]
+
+
+# ---------------------------------------------------------------- mosaic inference planning
+@pytest.mark.parametrize("h,w,tile,margin", [(100, 130, 64, 16), (64, 64, 64, 0), (97, 33, 32, 8), (2048, 2048, 512, 64),
+                                             (1, 1, 32, 0)])
+def test_mosaic_plan_covers_scene_exactly_once(h, w, tile, margin):
+    import numpy as np
+    from oracle.mosaic_oracle import tile_origins, write_tile
+    from s2lc_b200.inference import plan_mosaic
+    origins = plan_mosaic(h, w, tile, margin)
+    assert origins.dtype == torch.int32 and np.array_equal(origins.numpy(), tile_origins(h, w, tile, margin))
+    hits = np.zeros((h, w), dtype=np.int32)
+    keep = tile - 2 * margin
+    for t, l in origins.tolist():
+        y0, x0 = max(t + margin, 0), max(l + margin, 0)
+        hits[y0:min(t + margin + keep, h), x0:min(l + margin + keep, w)] += 1
+    assert (hits == 1).all()
+    # the oracle writer agrees with that geometry: constant-class tiles fill the whole mosaic
+    mosaic = np.full((h, w), 255, dtype=np.uint8)
+    if h * w <= 20000:
+        logits = np.zeros((3, tile, tile), dtype=np.float32)
+        logits[2] = 1.0
+        for t, l in origins.tolist():
+            write_tile(mosaic, logits, t, l, margin)
+        assert (mosaic == 2).all()
+
+
+def test_mosaic_plan_rejects_bad_geometry():
+    from s2lc_b200.inference import plan_mosaic, rank_batches
+    for args in [(64, 64, 48, 0), (64, 64, 64, 32), (64, 64, 64, -1), (0, 64, 64, 0)]:
+        with pytest.raises(ValueError):
+            plan_mosaic(*args)
+    with pytest.raises(ValueError):
+        rank_batches(10, 4, 2, 2)
+
+
+@pytest.mark.parametrize("n_tiles,batch,world", [(25, 8, 1), (25, 8, 2), (7, 8, 4), (64, 8, 8), (0, 4, 2)])
+def test_rank_batches_partition_the_tiles(n_tiles, batch, world):
+    from s2lc_b200.inference import rank_batches
+    seen = []
+    per_rank = []
+    for r in range(world):
+        mine = rank_batches(n_tiles, batch, r, world)
+        per_rank.append(len(mine))
+        for s, e in mine:
+            assert 0 < e - s <= batch
+            seen.extend(range(s, e))
+    assert sorted(seen) == list(range(n_tiles))
+    assert max(per_rank) - min(per_rank) <= 1
