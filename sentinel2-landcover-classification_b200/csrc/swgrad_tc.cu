@@ -70,7 +70,7 @@ __device__ __forceinline__ WUnit wunit_geom(const WgradArgs& P, const WPlan& K, 
     g.n = t / K.HS;
     g.h0 = hs * K.RU;
     g.rows = (P.H - g.h0) < K.RU ? (P.H - g.h0) : K.RU;
-    g.w0 = ws * 128;
+    g.w0 = ws * K.lines;
     g.m0 = 0;
     g.nload = g.rows + 2;
     g.nout = g.rows;
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
         const int hr = c.ug.h0 - 1 + c.j;
         arow0 = ((int64_t)c.ug.n * P.H + hr) * P.W + c.ug.w0 - 1;
         lo = c.ug.w0 == 0 ? 1 : 0;
-        hi = c.ug.w0 + 128 == P.W ? 128 : 129;
+        hi = c.ug.w0 + K.lines == P.W ? K.lines : K.lines + 1;
         if (hr < 0 || hr >= P.H) { lo = 1; hi = 0; }
         grow0 = arow0 + 1;                                    // G row = the output row h0 + j - 1
         gok = c.j >= 1 && c.j <= c.ug.rows;
@@ -472,33 +472,45 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
   K.CWg = A.Cout / 8;
   int ctas = kNumSMs;
   if (K.taps == 9) {
-    if (A.W % 128 != 0 || A.Cout > 128) return 1;
-    K.nsplit = (Ca + 47) / 48;
-    K.asplit = K.nsplit; K.g_w = A.Cout;
-    K.nt = sw_up((Ca + K.nsplit - 1) / K.nsplit, 8);
+    if (A.W % 32 != 0 || (A.Cout > 128 && A.Cout % 128 != 0)) return 1;
+    // G (output channels) sits on the 128 TMEM lanes: layers wider than 128 are cut into G slices of 128 channels,
+    // A (input channels) into slices of <= 48 (nine accumulators share the 512 TMEM columns).  One CTA = one
+    // (A slice, G slice) pair over its share of the pixel strips.
+    const int gsplit = (A.Cout + 127) / 128;
+    K.asplit = (Ca + 47) / 48;
+    K.nsplit = K.asplit * gsplit;
+    if (K.nsplit > kNumSMs) return 1;
+    K.g_w = A.Cout < 128 ? A.Cout : 128;
+    K.CWg = K.g_w / 8;
+    K.nt = sw_up((Ca + K.asplit - 1) / K.asplit, 8);
     K.Npad = sw_up(K.nt, 16);
     if (9 * K.Npad > 512) return 1;
     K.CWa = K.nt / 8;
-    K.lines = 128; K.a_lines = 130;
-    K.a_stride = 17 * 1024; K.a_slot = 17 * 1024;                 // one 64-channel chunk (nt <= 48)
-    K.g_stride = 16 * 1024;
     K.g_lbo = A.Cout <= 64 ? 1 : 0;                                 // narrow G: upper 64 lanes read the zero chunk
-    K.g_slot = K.g_lbo ? 16 * 1024 : 32 * 1024;
-    K.zslot = A.g.z ? 128 * K.CWg * 16 : 0;
     K.m_on_g = 1; K.n_mtiles = 1; K.nacc = 9;
+    // strip width = pixels per ring slot: the widest of 128 / 64 / 32 that divides W and whose rings fit shared memory
     bool ok = false;
-    for (int slack = 1; slack >= 0 && !ok; --slack) {   // a slot of slack matters more than a deeper prefetch
-      for (int pf = 2; pf >= 1 && !ok; --pf) {
-        const int ra = pf + 3 + slack, rg = pf + 2 + slack;
-        if (ra > SW_MAX_RING || rg > SW_MAX_RING) continue;
-        if (fixed + ra * K.a_slot + rg * K.g_slot + (K.g_lbo ? 16384 : 0) + (pf + 1) * K.zslot <= budget) {
-          K.pf = pf; K.ringA = ra; K.ringG = rg; ok = true;
+    for (int L = 128; L >= 32 && !ok; L >>= 1) {
+      if (A.W % L != 0) continue;
+      K.lines = L; K.a_lines = L + 2;
+      K.a_slot = sw_up((L + 2) * 128, 1024);                        // one 64-channel chunk (nt <= 48)
+      K.a_stride = K.a_slot;
+      K.g_stride = L * 128;
+      K.g_slot = K.g_lbo ? L * 128 : 2 * L * 128;
+      K.zslot = A.g.z ? L * K.CWg * 16 : 0;
+      for (int slack = 1; slack >= 0 && !ok; --slack) {   // a slot of slack matters more than a deeper prefetch
+        for (int pf = (L < 128 ? 3 : 2); pf >= 1 && !ok; --pf) {
+          const int ra = pf + 3 + slack, rg = pf + 2 + slack;
+          if (ra > SW_MAX_RING || rg > SW_MAX_RING) continue;
+          if (fixed + ra * K.a_slot + rg * K.g_slot + (K.g_lbo ? 16384 : 0) + (pf + 1) * K.zslot <= budget) {
+            K.pf = pf; K.ringA = ra; K.ringG = rg; ok = true;
+          }
         }
       }
     }
     if (!ok) return 1;
     ctas = kNumSMs / K.nsplit;
-    K.WS = A.W / 128;
+    K.WS = A.W / K.lines;
     int64_t best_cost = -1;
     for (int ru = 8; ru <= 128; ru *= 2) {
       const int r = ru < A.H ? ru : A.H;
@@ -570,8 +582,9 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
   while (K.tmem_cols < K.nacc * K.Npad) K.tmem_cols *= 2;
   if (K.units < ctas) ctas = K.units;
   K.ctas_per_slice = ctas;
-  const size_t smem = (size_t)fixed + (size_t)K.ringA * K.a_slot + (size_t)K.ringG * K.g_slot +
-                      (K.g_lbo ? 16384 : 0) + (size_t)(K.pf + 1) * K.zslot;
+  size_t smem = (size_t)fixed + (size_t)K.ringA * K.a_slot + (size_t)K.ringG * K.g_slot +
+                (K.g_lbo ? 16384 : 0) + (size_t)(K.pf + 1) * K.zslot;
+  if (smem < 120 * 1024) smem = 120 * 1024;   // one CTA per SM always: each CTA may hold all 512 TMEM columns
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(swgrad_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);

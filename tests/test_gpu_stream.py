@@ -121,7 +121,12 @@ def _run_wgrad(lib, mode, lz, lg, n, h, w, cin, cout, shape, bias):
 
 
 @pytest.mark.parametrize("cin,cbuf,cout,n,h,w", [(38, 40, 32, 2, 12, 128), (32, 32, 32, 1, 70, 256), (88, 88, 64, 2, 10, 128),
-                                                 (64, 64, 64, 3, 5, 256), (128, 128, 64, 1, 9, 128)])
+                                                 (64, 64, 64, 3, 5, 256), (128, 128, 64, 1, 9, 128),
+                                                 # deep decoder levels: strips of 64 / 32 px, G slices of 128 channels
+                                                 (168, 168, 128, 2, 24, 128), (128, 128, 128, 2, 128, 128),
+                                                 (320, 320, 256, 2, 64, 64), (256, 256, 256, 1, 40, 64),
+                                                 (640, 640, 512, 2, 32, 32), (512, 512, 512, 3, 32, 32),
+                                                 (64, 64, 64, 2, 32, 64), (96, 96, 88, 1, 17, 32)])
 def test_stream_wgrad3x3(lib, cin, cbuf, cout, n, h, w):
     """3x3 weight gradient, both operands lazy (BatchNorm+ReLU on A, BatchNorm-backward affine on G) + bias gradient."""
     rows = n * h * w
