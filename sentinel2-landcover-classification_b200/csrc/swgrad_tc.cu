@@ -18,7 +18,9 @@
 //         N = the CTA's slice of <= 48 input channels, 9 accumulators of N columns.
 //   1x1 : units are tiles of 128 / 64 / 32 pixels; the wider operand sits on M in up to 4 tiles of 128 channels,
 //         the narrower one on N; one accumulator per M tile.
-// Roles: warps 0-6 producers, warp 7 MMA issuer (converged warp, elected lane), warps 8-15 epilogue.
+// Roles: warps 0-14 producers (the in-place transforms are issue-latency bound: 7 producer warps left the SM's four
+// schedulers half empty and a ring slot took ~6k cycles whatever its length), warp 15 MMA issuer (converged warp,
+// elected lane); when the stream ends producer warps 0-7 become the epilogue.
 #include <cstdlib>
 
 #include "conv_common.cuh"
@@ -28,11 +30,11 @@ namespace s2lc {
 
 using namespace tc;
 
-constexpr int SW_PROD_WARPS = 7;
+constexpr int SW_PROD_WARPS = 15;
 constexpr int SW_PROD_THREADS = SW_PROD_WARPS * 32;
 constexpr int SW_MMA_WARP = SW_PROD_WARPS;
-constexpr int SW_EPI_WARP0 = SW_PROD_WARPS + 1;
-constexpr int SW_THREADS = (SW_PROD_WARPS + 1 + 8) * 32;
+constexpr int SW_EPI_WARPS = 8;          // producer warps 0-7 drain TMEM once their stream has ended
+constexpr int SW_THREADS = (SW_PROD_WARPS + 1) * 32;
 constexpr int SW_MAX_RING = 8;
 
 struct WPlan {
@@ -418,9 +420,10 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
       if (leader) umma_commit(done);
       __syncwarp();
     }
-  } else {
+  }
+  if (warp < SW_EPI_WARPS) {
     // ================================================================== epilogue: once, after the last MMA
-    const int ew = warp - SW_EPI_WARP0, half = ew >> 2, q = warp & 3;
+    const int half = warp >> 2, q = warp & 3;
     mbar_wait(done, 0);
     tc_fence_after();
     const int mrow = q * 32 + lane;
