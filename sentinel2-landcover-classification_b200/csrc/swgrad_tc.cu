@@ -56,6 +56,7 @@ struct WPlan {
   int tmem_cols;
   int g_lbo;           // 3x3: 0 = G slot has 2 chunks; else G slot has 1 chunk and the upper lanes read the zero chunk
   int RU, HS, WS, units, ctas_per_slice;
+  int children, lw;    // transposed conv: 4 children (2x2 output positions), each its own CTA set; lw = log2(W)
 };
 
 struct WUnit {
@@ -78,7 +79,7 @@ __device__ __forceinline__ WUnit wunit_geom(const WgradArgs& P, const WPlan& K, 
     g.nout = g.rows;
   } else {
     g.m0 = (int64_t)u * K.lines;
-    g.n = (int)(g.m0 / ((int64_t)P.H * P.W));
+    g.n = (int)((uint32_t)g.m0 / (uint32_t)(P.H * P.W));      // M < 2^31 (checked by the host)
     g.h0 = 0; g.rows = 1; g.w0 = 0;
     g.nload = 1;
     g.nout = 1;
@@ -109,7 +110,10 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int slice = blockIdx.x % K.nsplit, cta = blockIdx.x / K.nsplit;
+  const int nsl = K.nsplit * K.children;
+  const int sl = blockIdx.x % nsl, cta = blockIdx.x / nsl;
+  const int child = sl / K.nsplit, slice = sl - child * K.nsplit;      // child = 2*qy + qx of a transposed conv
+  const int qy = child >> 1, qx = child & 1;
   const int a_c0 = (slice % K.asplit) * K.nt;                      // first input channel of this CTA's A slice
   const int g_c0 = (slice / K.asplit) * K.g_w;                     // first output channel of its G slice
   constexpr int R = TAPS == 9 ? 3 : 1;
@@ -171,6 +175,8 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
     const bool a_aff = P.a.scale != nullptr;
     const bool a_xf = a_aff || gate != nullptr || act != S2LC_ACT_NONE;
     const bool do_bias = P.dbias != nullptr && (slice % K.asplit) == 0;
+    const bool is_ct = P.mode == S2LC_CONVT_FWD;
+    const int HWi = P.H * P.W;
     const bool g_xf = z_ptr != nullptr || rowscale != nullptr || do_bias;
     // fixed chunk per thread, separately for the A part and the G part of a load
     const int dla = SW_PROD_THREADS / CWa, nact_a = dla * CWa;
@@ -225,14 +231,25 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
       if (gok) {
         const uint32_t sG = ringG_u32 + (uint32_t)(ig * K.g_slot) + dst_cg;
         const uint32_t zG = z_u32 + (uint32_t)(iz * K.zslot) + (uint32_t)tid * 16u;
+        // transposed conv: input pixel (n, h, w) pairs with the gradient row of its child (n, 2h+qy, 2w+qx)
+        int pi0 = 0;
+        if (is_ct) {
+          pi0 = (int)(c.ug.m0 - (int64_t)c.ug.n * HWi);
+          grow0 = (int64_t)c.ug.n * 4 * HWi;
+        }
         const bf16* dbase = dy_ptr + grow0 * g_ld + g_c0 + chg * 8;
         const bf16* zbase = z_ptr ? z_ptr + grow0 * g_ld + g_c0 + chg * 8 : nullptr;
         line = lg0;
 #pragma unroll 2
         for (int i = 0; i < nit_g; ++i, line += dlg) {
           const uint32_t dst = sG + (uint32_t)(line * 128) + ((chg7 ^ (uint32_t)(line & 7)) << 4);
-          cp_async16(dst, dbase + line * g_ld);
-          if (zbase) cp_async16(zG + (uint32_t)(i * nact_g) * 16u, zbase + line * g_ld);
+          int roff = line;
+          if (is_ct) {
+            const int pi = pi0 + line;
+            roff = (2 * (pi >> K.lw) + qy) * (2 * P.W) + 2 * (pi & (P.W - 1)) + qx;
+          }
+          cp_async16(dst, dbase + roff * g_ld);
+          if (zbase) cp_async16(zG + (uint32_t)(i * nact_g) * 16u, zbase + roff * g_ld);
         }
       }
       cp_async_commit();
@@ -424,6 +441,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
   if (warp < SW_EPI_WARPS) {
     // ================================================================== epilogue: once, after the last MMA
     const int half = warp >> 2, q = warp & 3;
+    const int ct_base = P.mode == S2LC_CONVT_FWD ? child * P.Cout : 0;   // convT: gradient row = (child, co)
     mbar_wait(done, 0);
     tc_fence_after();
     const int mrow = q * 32 + lane;
@@ -441,7 +459,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
           const int co = gl + g_c0, ci = al + a_c0;
           // rows / columns beyond the slice widths belong to another CTA (and are zero here)
           if (gl < K.g_w && al < K.nt && co < P.Cout && ci < P.Cin)
-            atomicAdd(P.dw + wgrad_index(P, co, tap * P.Cin + ci), v[j]);
+            atomicAdd(P.dw + wgrad_index(P, ct_base + co, tap * P.Cin + ci), v[j]);
         }
       }
     }
@@ -460,7 +478,12 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     const char* e = getenv("S2LC_NO_STREAM");   // test hook: compare against the slab engine
     if (e && e[0] == '1') return 1;
   }
-  if (A.dtype != S2LC_BF16 || (A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONV_1X1)) return 1;
+  if (A.dtype != S2LC_BF16 || (A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONV_1X1 && A.mode != S2LC_CONVT_FWD)) return 1;
+  const int children = A.mode == S2LC_CONVT_FWD ? 4 : 1;
+  int lw = 0;
+  while ((1 << lw) < A.W) ++lw;
+  if (children == 4 && ((1 << lw) != A.W || A.a.gate || A.g.rowscale)) return 1;   // row arithmetic by shifts
+  if ((int64_t)A.N * A.H * A.W * children >= (1ll << 31)) return 1;
   const int Ca = sw_up(A.Cin, 8);
   if (A.Cout % 8 != 0 || A.a.ld < Ca || A.a.ld % 8 != 0 || A.g.ld_dy % 8 != 0) return 1;
   if (!sw_aligned16(A.a.raw) || !sw_aligned16(A.g.dy)) return 1;
@@ -542,13 +565,13 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
         const int ncta = sw_up((cn + ns - 1) / ns, 8);
         if ((cn + ncta - 1) / ncta != ns) continue;
         const int npad = sw_up(ncta, 16);
-        if (npad > 256 || n_mt * npad > 512 || ms * ns > kNumSMs) continue;
+        if (npad > 256 || n_mt * npad > 512 || ms * ns * children > kNumSMs) continue;
         if (A.dbias && (K.m_on_g ? mcta : ncta) > 256) continue;
         const int cw_m = (mcta < cm ? mcta : sw_up(cm, 8)) / 8, cw_n = ncta / 8;
         if (cw_m > SW_PROD_THREADS || cw_n > SW_PROD_THREADS) continue;
         const int chunks_m = 2 * n_mt, chunks_n = (npad + 63) / 64;
         const int cwg = K.m_on_g ? cw_m : cw_n;
-        const int kslabs = kNumSMs / (ms * ns);
+        const int kslabs = kNumSMs / (ms * ns * children);
         for (int lines = 128; lines >= 32; lines /= 2) {
           if (HW % lines != 0 || M / lines < 2 * kslabs) continue;
           const int slot = (chunks_m + chunks_n) * lines * 128;
@@ -579,8 +602,9 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     K.g_lbo = 0;
     K.RU = 1; K.HS = 1; K.WS = 1;
     K.units = (int)(M / K.lines);
-    ctas = kNumSMs / K.nsplit;
+    ctas = kNumSMs / (K.nsplit * children);
   }
+  K.children = children; K.lw = lw;
   K.tmem_cols = 32;
   while (K.tmem_cols < K.nacc * K.Npad) K.tmem_cols *= 2;
   if (K.units < ctas) ctas = K.units;
@@ -599,7 +623,7 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     attr_set = true;
   }
   if (K.taps == 9) swgrad_kernel<9><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
-  else swgrad_kernel<1><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
+  else swgrad_kernel<1><<<ctas * K.nsplit * K.children, SW_THREADS, smem, st>>>(A, K);
   return check_launch("swgrad_tc");
 }
 

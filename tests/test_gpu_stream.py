@@ -160,3 +160,21 @@ def test_stream_wgrad1x1(lib, cin, cout, n, h, w, gated):
     lg = L().LazyGrad(dy.data_ptr(), cout, z.data_ptr(), cout, p_.data_ptr(), q_.data_ptr(), t_.data_ptr(), rsc.data_ptr())
     (rw, _), (gw, _) = _both(lambda: _run_wgrad(lib, 0, lz, lg, n, h, w, cin, cout, (cout, cin, 1, 1), False))
     assert rel_err(gw, rw) < 1e-3
+
+
+@pytest.mark.parametrize("cin,cout,n,h,w,bnz", [(64, 32, 2, 256, 256, True), (128, 64, 2, 128, 128, True),
+                                                (256, 128, 2, 64, 64, True), (512, 256, 3, 32, 32, False),
+                                                (2048, 512, 4, 16, 16, True)])
+def test_stream_wgradT(lib, cin, cout, n, h, w, bnz):
+    """2x2 stride-2 transposed-conv weight + bias gradient: input pixel (n, h, w) pairs with the gradient rows of its
+    four children (n, 2h+qy, 2w+qx); lazy BatchNorm+ReLU on A, BatchNorm-backward affine on G."""
+    rows = n * h * w
+    x = mk((rows, cin), 151).to(BF)
+    sc, sh = 1 + 0.1 * mk((cin,), 152), 0.1 * mk((cin,), 153)
+    lz = lazy(x, cin, sc, sh, act=2)
+    dy, z = mk((rows * 4, cout), 154).to(BF), mk((rows * 4, cout), 155).to(BF)
+    p_, q_, t_ = 1 + 0.1 * mk((cout,), 156), 0.05 * mk((cout,), 157), 0.01 * mk((cout,), 158)
+    lg = lazygrad(dy, cout, z, p_, q_, t_) if bnz else lazygrad(dy, cout)
+    (rw, rb), (gw, gb) = _both(lambda: _run_wgrad(lib, 2, lz, lg, n, h, w, cin, cout, (cin, cout, 2, 2), True))
+    assert rel_err(gw, rw) < 1e-3
+    assert rel_err(gb, rb) < 1e-3
