@@ -211,6 +211,11 @@ int32_t s2lc_loss_fwd_bwd(const void* logits, int64_t ld, const int64_t* y, cons
                           float label_smoothing, int64_t ignore_index, int32_t kind, int32_t reduce_mean,
                           float* loss_out, float* wsum_scratch, void* dlogits, int64_t ld_d, int64_t rows,
                           int32_t n_classes, int32_t dtype, void* stream);
+/* Materialise a lazy gradient: out[row, c] = p[c]*dy[row, c]*rowscale[row / HW] + q[c]*z[row, c] + t[c], same fp32
+ * formula and rounding as the conv engines' operand loaders (autograd of BatchNorm2d behind the decoder 3x3 convs,
+ * efficientnet_unet.py:168-176).  `out` may alias g->dy.                                                           */
+int32_t s2lc_lazygrad_apply(const s2lc_lazygrad* g, void* out, int64_t ld_out, int64_t rows, int32_t C, int32_t HW,
+                            int32_t dtype, void* stream);
 int32_t s2lc_scale_inplace(void* x, int64_t ld, const float* factor_dev, int64_t rows, int32_t C, int32_t dtype,
                            void* stream);
 

@@ -14,6 +14,7 @@ Design (B200-first):
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -21,6 +22,8 @@ from . import _lib as L
 from .efficientnet_unet import BlockSpec, EfficientnetUnet
 
 _DT = {torch.float32: L.F32, torch.bfloat16: L.BF16}
+# A/B switch for the decoder's materialised BatchNorm-backward gradients (see Workspace.materialize_grad)
+MATERIALIZE_DECODER_GRADS = os.environ.get("S2LC_MATERIALIZE", "1") != "0"
 
 
 def _up(x: int, m: int) -> int:
@@ -192,6 +195,13 @@ class Workspace:
                        rowscale if isinstance(rowscale, (int, type(None))) else rowscale.data_ptr())
         self._keep.append(g)
         return g
+
+    def materialize_grad(self, g: L.LazyGrad, dy, ld: int, rows: int, c: int, hw: int) -> L.LazyGrad:
+        """g = p*dy + q*z + t written once over ``dy`` (s2lc_lazygrad_apply) and handed on as a plain gradient: the
+        decoder 3x3 layers cut their channels over many CTAs in both gradient engines, each of which would redo the
+        transform on its copy of the operand."""
+        self.B("s2lc_lazygrad_apply", C.byref(g), dy.data_ptr(), ld, rows, c, hw, self.dt, nbytes=3 * rows * c * self.es)
+        return self.lazygrad(dy, ld)
 
     def F(self, name: str, *args, nbytes: float = 0, flops: float = 0) -> None:
         self.fwd_list.append((getattr(self.lib, name), args))
@@ -536,6 +546,8 @@ class Workspace:
                 dyB = lv.dyB_buf            # filled by the level above (convT dgrad)
             self.bn_backward(lv.bnB, lv.kdc + ".4")
             gB = self.lazygrad(dyB, co, lv.zc2, co, lv.bnB)
+            if MATERIALIZE_DECODER_GRADS:
+                gB = self.materialize_grad(gB, dyB, co, lv.rows, co, lv.h * lv.w)
             self.wgrad(L.CONV_3X3, lv.a1, gB, N, lv.h, lv.w, co, co, self.gptr(lv.kdc + ".3.weight"),
                        self.gptr(lv.kdc + ".3.bias"))
             dyA = self.act(lv.rows, co)
@@ -545,6 +557,8 @@ class Workspace:
                       stats=("SB", lv.bnA.st_b), stats_kind=L.STATS_BNBWD)
             self.bn_backward(lv.bnA, lv.kdc + ".1")
             gA = self.lazygrad(dyA, co, lv.zc1, co, lv.bnA)
+            if MATERIALIZE_DECODER_GRADS:
+                gA = self.materialize_grad(gA, dyA, co, lv.rows, co, lv.h * lv.w)
             self.wgrad(L.CONV_3X3, lv.cat_lazy, gA, N, lv.h, lv.w, lv.c_cat, co, self.gptr(lv.kdc + ".0.weight"),
                        self.gptr(lv.kdc + ".0.bias"))
             n_in_used = lv.c_up if lv.last else lv.c_cat    # d(input tile) is not needed

@@ -68,6 +68,7 @@ _PROTOS = {
     "s2lc_dwconv_fwd_tile": ([C.POINTER(Lazy), vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp], i32),
     "s2lc_prepare_batch": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, vp], i32),
     "s2lc_argmax_confusion": ([vp, i64, vp, vp, vp, i64, i32, i32, vp], i32),
+    "s2lc_lazygrad_apply": ([C.POINTER(LazyGrad), vp, i64, i64, i32, i32, i32, vp], i32),
     "s2lc_gather_tiles": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, vp], i32),
     "s2lc_argmax_mosaic": ([vp, i64, vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, vp], i32),
     "s2lc_se_pool": ([C.POINTER(Lazy), vp, i32, i32, i32, i32, vp], i32),

@@ -658,6 +658,41 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
 }
 
+// ------------------------------------------------------------------------------------------ lazy gradient -> tensor
+// g = p*dy*rowscale + q*z + t written out once (in place over dy is allowed).  Used in front of the compute-heavy
+// decoder 3x3 layers: their weight- and data-gradient engines split the channels over many CTAs, each of which would
+// otherwise redo this transform on its copy of the operand (3-14x per element), and those producers are
+// instruction-bound, not HBM-bound.  Same fp32 formula and the same single rounding as the engines' loaders.
+template <typename T>
+__global__ void __launch_bounds__(256) lazygrad_apply_kernel(s2lc_lazygrad g, T* __restrict__ out, int64_t ld_out,
+                                                             int64_t rows, int C, int HW) {
+  const int CV = C / 8;
+  const int64_t total = rows * CV;
+  const T* dy = reinterpret_cast<const T*>(g.dy);
+  const T* z = reinterpret_cast<const T*>(g.z);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / CV;
+    const int c = (int)(i - r * CV) * 8;
+    float v[8];
+    Vec8<T>::load(dy + r * g.ld_dy + c, v);
+    if (g.rowscale) {
+      const float rs = __ldg(g.rowscale + r / HW);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] *= rs;
+    }
+    if (z) {
+      float zz[8], pp[8], qq[8], tt[8];
+      Vec8<T>::load(z + r * g.ld_z + c, zz);
+      Vec8<float>::load(g.p + c, pp);
+      Vec8<float>::load(g.q + c, qq);
+      Vec8<float>::load(g.t + c, tt);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaf(pp[j], v[j], fmaf(qq[j], zz[j], tt[j]));
+    }
+    Vec8<T>::store(out + r * ld_out + c, v);
+  }
+}
+
 static inline int grid_for(int64_t work_items, int per_block, int max_blocks = kNumSMs * 8) {
   int64_t b = (work_items + per_block - 1) / per_block;
   if (b < 1) b = 1;
@@ -783,6 +818,19 @@ int32_t s2lc_bn_bwd_reduce(const void* dy, int64_t ld_dy, const void* z, int64_t
                                                (cudaStream_t)stream>>>((const T*)dy, ld_dy, (const T*)z, ld_z,
                                                                        rowscale, stats, rows, C, HW)));
   return check_launch("bn_bwd_reduce");
+}
+
+int32_t s2lc_lazygrad_apply(const s2lc_lazygrad* g, void* out, int64_t ld_out, int64_t rows, int32_t C, int32_t HW,
+                            int32_t dtype, void* stream) {
+  S2LC_REQUIRE(g != nullptr && g->dy != nullptr && out != nullptr, S2LC_ERR_SHAPE, "lazygrad_apply: null pointer");
+  S2LC_REQUIRE(C % 8 == 0 && g->ld_dy % 8 == 0 && ld_out % 8 == 0 && (!g->z || g->ld_z % 8 == 0), S2LC_ERR_ALIGN,
+               "lazygrad_apply: alignment (C=%d)", C);
+  S2LC_REQUIRE(!g->z || (g->p && g->q && g->t), S2LC_ERR_SHAPE, "lazygrad_apply: z needs p, q, t");
+  S2LC_REQUIRE(HW > 0, S2LC_ERR_SHAPE, "lazygrad_apply: HW");
+  if (rows == 0) return S2LC_OK;
+  DISPATCH_T(dtype, (lazygrad_apply_kernel<T><<<grid_for(rows * (C / 8), 256, kNumSMs * 8), 256, 0,
+                                                (cudaStream_t)stream>>>(*g, (T*)out, ld_out, rows, C, HW)));
+  return check_launch("lazygrad_apply");
 }
 
 static inline int se_splits(int N, int HW, int C, int blocks_per_sm = SE_BLOCKS_PER_SM) {
