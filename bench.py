@@ -19,9 +19,16 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# NCCL writes its "NCCL version ..." banner to STDOUT at NCCL_DEBUG=VERSION; stdout must carry ONE JSON line
-if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-    os.environ["NCCL_DEBUG"] = "WARN"
+# stdout must carry exactly ONE JSON line, but libraries write there too (NCCL prints its "NCCL version ..." banner to
+# fd 1 at every NCCL_DEBUG level >= VERSION, which includes WARN): keep the real stdout aside for the result line and
+# point fd 1 at stderr for everything else.
+_RESULT_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(result: dict) -> None:
+    os.write(_RESULT_FD, (json.dumps(result) + "\n").encode())
+
 
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
@@ -129,7 +136,7 @@ def run_reference(a) -> None:
     v = bs / dt
     cores = torch.get_num_threads()
     sample = f"{a.steps} steps of 1 tile {a.size}x{a.size} fp32 fwd+focal+bwd+Adam (oracle port of the reference modules)"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "train_tiles_per_s", "value": v, "unit": "tiles/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -138,7 +145,7 @@ def run_reference(a) -> None:
                    "os_cpu_count": os.cpu_count(), "torch": torch.__version__},
         "cpu_baseline": {"value": v, "unit": "tiles/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "tiles/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def main() -> None:
@@ -253,7 +260,7 @@ def main() -> None:
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
 
 
 def kernel_breakdown(trainer, model, ws, x, y) -> dict:
