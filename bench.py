@@ -126,6 +126,12 @@ def run_reference(a) -> None:
     if rank != 0:
         return
     bs = 1   # bounded sample: one 512x512 tile per step of the same workload
+    # all the host cores this process may use (torchrun exports OMP_NUM_THREADS=1 for its workers)
+    try:
+        ncpu = len(os.sched_getaffinity(0))
+    except AttributeError:
+        ncpu = os.cpu_count() or 1
+    torch.set_num_threads(max(ncpu, 1))
     step = cpu_reference_step_fn(a.version, a.size, bs)
     for _ in range(max(a.warmup, 1)):
         step()
