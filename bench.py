@@ -304,9 +304,14 @@ def breakdown_table(agg: dict) -> list:
 
 
 # kernel-class label -> CUDA kernel behind it (for the ncu cross-reference in profiles/)
-KERNEL_OF = {"conv1x1_wgrad": "wgrad_tc_kernel<1,4,4>", "conv3x3_wgrad": "wgrad_tc_kernel<9,2,1>",
-             "convT_wgrad": "wgrad_tc_kernel<1,4,4>", "conv3x3": "conv_tc_kernel", "conv3x3_dgrad": "conv_tc_kernel",
-             "conv1x1": "conv_tc_kernel", "conv1x1_dgrad": "conv_tc_kernel", "dwconv_fwd": "dw2::dw2_fwd_kernel",
+KERNEL_OF = {"conv1x1_wgrad": "swgrad_kernel<1,false> (streaming; wgrad_tc_kernel for the shapes it declines)",
+             "conv3x3_wgrad": "swgrad_kernel<9,false> (streaming, every decoder level)",
+             "convT_wgrad": "swgrad_kernel<1,true> (streaming, four children)",
+             "conv3x3": "sconv_kernel<9,*> (W % 128 == 0) / conv_tc_kernel<2>",
+             "conv3x3_dgrad": "sconv_kernel<9,*> (W % 128 == 0) / conv_tc_kernel<2>",
+             "conv1x1": "sconv_kernel<1,*> (shallow) / conv_tc_kernel<2> (deep)",
+             "conv1x1_dgrad": "sconv_kernel<1,*> (shallow) / conv_tc_kernel<2> (deep)",
+             "dwconv_fwd": "dw2::dw2_fwd_kernel",
              "dwconv_bwd": "dw2::dw2_bwd_kernel (fused data + weight gradient)"}
 
 

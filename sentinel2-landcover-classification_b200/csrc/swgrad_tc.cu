@@ -93,7 +93,7 @@ struct WCursor {
   WUnit ug;
 };
 
-template <int TAPS>
+template <int TAPS, bool CT>   // CT: 2x2 transposed conv (1x1 path with strided gradient rows, four children)
 __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPlan K) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
     const bool a_aff = P.a.scale != nullptr;
     const bool a_xf = a_aff || gate != nullptr || act != S2LC_ACT_NONE;
     const bool do_bias = P.dbias != nullptr && (slice % K.asplit) == 0;
-    const bool is_ct = P.mode == S2LC_CONVT_FWD;
+    constexpr bool is_ct = CT;
     const int HWi = P.H * P.W;
     const bool g_xf = z_ptr != nullptr || rowscale != nullptr || do_bias;
     // fixed chunk per thread, separately for the A part and the G part of a load
@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
   if (warp < SW_EPI_WARPS) {
     // ================================================================== epilogue: once, after the last MMA
     const int half = warp >> 2, q = warp & 3;
-    const int ct_base = P.mode == S2LC_CONVT_FWD ? child * P.Cout : 0;   // convT: gradient row = (child, co)
+    const int ct_base = CT ? child * P.Cout : 0;   // convT: gradient row = (child, co)
     mbar_wait(done, 0);
     tc_fence_after();
     const int mrow = q * 32 + lane;
@@ -614,16 +614,18 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
   if (smem < 120 * 1024) smem = 120 * 1024;   // one CTA per SM always: each CTA may hold all 512 TMEM columns
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(swgrad_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(swgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(swgrad_kernel<9, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(swgrad_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(swgrad_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("swgrad_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return S2LC_ERR_CUDA;
     }
     attr_set = true;
   }
-  if (K.taps == 9) swgrad_kernel<9><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
-  else swgrad_kernel<1><<<ctas * K.nsplit * K.children, SW_THREADS, smem, st>>>(A, K);
+  if (K.taps == 9) swgrad_kernel<9, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
+  else if (children == 4) swgrad_kernel<1, true><<<ctas * K.nsplit * K.children, SW_THREADS, smem, st>>>(A, K);
+  else swgrad_kernel<1, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
   return check_launch("swgrad_tc");
 }
 
