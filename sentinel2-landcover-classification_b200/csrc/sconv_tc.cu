@@ -651,7 +651,9 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
     const int ncta = sc_up((n16 + ns - 1) / ns, 16);
     if (ncta > 256) continue;
     const int wb = K.taps * K.Kc * ncta * 128;
-    for (int ring = 6; ring >= R + 1; --ring) {
+    // 1x1: a ring of two whole-K slots leaves no load in flight behind the tile being multiplied (384->64 at 64x64 ran
+    // 2.3x slower than on the tile engine) -> at least three slots, else the tile engine takes the layer
+    for (int ring = 6; ring >= (K.taps == 9 ? R + 1 : 3); --ring) {
       int pf = ring - R - 1;          // one slot of slack so producers never wait on the tile they just fed
       if (pf > 3) pf = 3;
       if (pf < 1) pf = 1;
