@@ -534,6 +534,36 @@ def test_bn_apply_and_reduce(lib, prec):
     assert rel_err(st[c:], (d * nchw(zr, n, h, w).double()).sum((0, 2, 3))) < 1e-6
 
 
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("with_z,with_rs", [(True, False), (True, True), (False, True), (False, False)])
+def test_lazygrad_apply(lib, prec, with_z, with_rs):
+    """g = p*dy*rowscale + q*z + t written once (s2lc_lazygrad_apply), out of place and in place over dy: one fp32
+    fma chain + ONE rounding to the storage type -> bit-exact against the same chain in torch for fp32, 1 bf16 ulp
+    (2^-8 relative) for bf16."""
+    dtype, dt, tol = DT[prec]
+    n, c, h, w = 3, 40, 9, 11
+    dy, z = nhwc(mk((n, c, h, w), 91), dtype), nhwc(mk((n, c, h, w), 92), dtype)
+    p_, q_, t_ = 1 + 0.1 * mk((c,), 93), 0.05 * mk((c,), 94), 0.01 * mk((c,), 95)
+    rs = torch.tensor([0.0, 1.25, 0.8], device="cuda") if with_rs else None
+    g = lazygrad(dy, c, z, p_, q_, t_, rs) if with_z else lazygrad(dy, c, rs=rs)
+    out = torch.empty_like(dy)
+    L().check(lib.s2lc_lazygrad_apply(C.byref(g), out.data_ptr(), c, n * h * w, c, h * w, dt, stream()))
+    d = dy.float().view(n, h * w, c)
+    if with_rs:
+        d = d * rs.view(n, 1, 1)
+    want = d
+    if with_z:
+        want = torch.addcmul(torch.addcmul(t_.view(1, 1, c).expand_as(d), q_.view(1, 1, c), z.float().view(n, h * w, c)),
+                             p_.view(1, 1, c), d)
+    want = want.reshape(n * h * w, c)
+    assert rel_err(out.float(), want) <= (1e-6 if prec == "fp32" else 2 ** -8)
+    assert float((out.float() - want).abs().max()) <= (1e-5 if prec == "fp32" else 2 ** -7 * float(want.abs().max()))
+    keep = dy.clone()
+    L().check(lib.s2lc_lazygrad_apply(C.byref(g), dy.data_ptr(), c, n * h * w, c, h * w, dt, stream()))   # in place
+    assert torch.equal(dy, out)
+    del keep
+
+
 def test_loss_against_golden(golden_arrays):
     from s2lc_b200.losses import CrossEntropyLoss, FocalLoss
     from s2lc_b200 import synthetic
