@@ -31,12 +31,14 @@ namespace s2lc {
 
 using namespace tc;
 
-constexpr int SC_PROD_WARPS = 7;   // 7 + 1 MMA + 8 epilogue = 16 warps -> 128 registers per thread
-constexpr int SC_PROD_THREADS = SC_PROD_WARPS * 32;
-constexpr int SC_MMA_WARP = SC_PROD_WARPS;
-constexpr int SC_EPI_WARP0 = SC_PROD_WARPS + 1;
-constexpr int SC_EPI_WARPS = 8;
-constexpr int SC_THREADS = (SC_PROD_WARPS + 1 + SC_EPI_WARPS) * 32;
+// 16 warps -> 128 registers per thread.  Warp 15 issues the MMAs; warps [0, prod_warps) are producers and warps
+// [prod_warps, 15) form epilogue groups of four (one warp per TMEM lane quarter).  The split is a plan parameter:
+// 7 + 8 (two epilogue groups) by default, 3 + 12 (three groups) for thin-A / wide-N layers (1x1 expand convs), where
+// the producers finish a slot in a fraction of the time the epilogue needs for its 128 x N tile.
+constexpr int SC_WARPS = 16;
+constexpr int SC_MMA_WARP = SC_WARPS - 1;
+constexpr int SC_THREADS = SC_WARPS * 32;
+constexpr int SC_MAX_EGROUPS = 3;
 constexpr int SC_MAX_RING = 8;
 constexpr int SC_MAX_ACC = 4;
 constexpr int SC_MAX_ITEMS = 10;   // 16 B chunks per producer thread per slot: ceil(130 * 16 / 256) = 9
@@ -50,6 +52,7 @@ struct SPlan {
   int slot_bytes;    // Kc * chunk_stride
   int zslot_bytes;   // linear staging of z (BatchNorm-backward operand), 0 if unused
   int ring, pf;      // ring slots, prefetch distance (pf < ring - (3x3 ? 2 : 0))
+  int prod_warps;    // producer warps: 7 (two epilogue groups) or 3 (three epilogue groups, thin A / wide N)
   int nsplit;        // CTAs sharing a unit along N
   int Ncta;          // output channels per CTA (multiple of 16)
   int nacc;          // TMEM accumulators
@@ -114,8 +117,9 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
   unsigned char* zring = ring + K.ring * K.slot_bytes;         // [pf+1][zslot_bytes]
   float* svec = reinterpret_cast<float*>(zring + (K.pf + 1) * K.zslot_bytes);   // [3][Kc*64] operand affine vectors
   float* evec = svec + 3 * K.Kc * 64;                          // [3][256] epilogue vectors: bias, prev scale, prev shift
-  float* sstat = evec + 3 * 256;                               // [2 groups][2][256]
-  uint64_t* full = reinterpret_cast<uint64_t*>(sstat + 2 * 2 * 256);
+  const int sgroups = K.prod_warps == 3 ? SC_MAX_EGROUPS : 2;   // epilogue groups that own a statistics area
+  float* sstat = evec + 3 * 256;                               // [sgroups][2][256]
+  uint64_t* full = reinterpret_cast<uint64_t*>(sstat + sgroups * 2 * 256);
   uint64_t* empty = full + SC_MAX_RING;
   uint64_t* acc_full = empty + SC_MAX_RING;
   uint64_t* acc_empty = acc_full + SC_MAX_ACC;
@@ -127,11 +131,12 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
   constexpr int R = TAPS == 9 ? 3 : 1;
   const uint32_t ring_u32 = smem_u32(ring), w_u32 = smem_u32(wsm);
   const int nchunks = K.Ncta / 16;
-  const int egroups = nchunks < 2 ? nchunks : 2;
+  const int epi_groups = (SC_MMA_WARP - K.prod_warps) >> 2;
+  const int egroups = nchunks < epi_groups ? nchunks : epi_groups;
 
   // ------------------------------------------------------------------ one-time setup (all threads)
   if (tid == 0) {
-    for (int s = 0; s < K.ring; ++s) { mbar_init(&full[s], SC_PROD_WARPS); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < K.ring; ++s) { mbar_init(&full[s], (uint32_t)K.prod_warps); mbar_init(&empty[s], 1); }
     for (int b = 0; b < K.nacc; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4 * egroups); }
     fence_barrier_init();
   }
@@ -171,7 +176,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
       evec[256 + i] = (in && P.has_prev && P.prev.scale) ? P.prev.scale[col] : 1.f;
       evec[512 + i] = (in && P.has_prev && P.prev.scale) ? P.prev.shift[col] : 0.f;
     }
-    for (int i = tid; i < 2 * 2 * 256; i += SC_THREADS) sstat[i] = 0.f;
+    for (int i = tid; i < sgroups * 2 * 256; i += SC_THREADS) sstat[i] = 0.f;
   }
   fence_proxy_async();
   tc_fence_before();
@@ -193,7 +198,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
     }
   };
 
-  if (warp < SC_PROD_WARPS) {
+  if (warp < K.prod_warps) {
     // ================================================================== producers
     const bool is_grad = P.a_is_grad != 0;
     const bf16* a_ptr = reinterpret_cast<const bf16*>(is_grad ? P.a_bwd.dy : P.a_fwd.raw);
@@ -207,7 +212,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
     // every ACTIVE producer thread owns one fixed 8-channel chunk `ch` (so its affine vectors live in registers) and
     // walks the lines of a slot with stride dl
     const int CW = K.CW, nv = K.Kc * 64;
-    const int dl = SC_PROD_THREADS / CW, nact = dl * CW;
+    const int dl = (K.prod_warps * 32) / CW, nact = dl * CW;
     const bool active = tid < nact;
     const int line0 = tid / CW, ch = tid - line0 * CW;
     const int nit = active ? (K.lines - line0 + dl - 1) / dl : 0;   // lines this thread owns in every slot
@@ -399,9 +404,9 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
       }
     }
   } else {
-    // ================================================================== epilogue: 2 groups x 4 lane-quarter warps;
-    // group g owns the 16-column chunks cj = g, g+2, ... of EVERY tile.
-    const int ew = warp - SC_EPI_WARP0, grp = ew >> 2, q = warp & 3;   // q = TMEM lane quarter this warp may read
+    // ================================================================== epilogue: groups of 4 lane-quarter warps;
+    // group g owns the 16-column chunks cj = g, g+egroups, ... of EVERY tile.
+    const int ew = warp - K.prod_warps, grp = ew >> 2, q = warp & 3;   // q = TMEM lane quarter this warp may read
     if (grp < egroups) {
       float* gstat = sstat + grp * 512;                                 // [2][256] of this group
       const int gtid = (ew & 3) * 32 + lane;
@@ -579,7 +584,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan 
         for (int o = 0; o < ug.nout; ++o, orow += P.W) {
           mbar_wait(&acc_full[b], bph);
           tc_fence_after();
-          for (int cj = grp; cj < nchunks; cj += 2) {
+          for (int cj = grp; cj < nchunks; cj += egroups) {
             const int lc0 = cj * 16, col0 = n0 + lc0;
             const int nvalid = P.Nout - col0;
             if (nvalid <= 0) break;   // warp-uniform
@@ -651,9 +656,10 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
     const int ncta = sc_up((n16 + ns - 1) / ns, 16);
     if (ncta > 256) continue;
     const int wb = K.taps * K.Kc * ncta * 128;
-    // 1x1: a ring of two whole-K slots leaves no load in flight behind the tile being multiplied (384->64 at 64x64 ran
-    // 2.3x slower than on the tile engine) -> at least three slots, else the tile engine takes the layer
-    for (int ring = 6; ring >= (K.taps == 9 ? R + 1 : 3); --ring) {
+    // 1x1 with K > 256: a ring of two 80-96 KB whole-K slots leaves no load in flight behind the tile being multiplied
+    // (384->64 at 64x64 ran 2.3x slower than on the tile engine) -> the tile engine takes those; up to K = 256 two
+    // slots still beat it (240->40 at 128x128: 0.19 vs 0.25 ms)
+    for (int ring = 6; ring >= (K.taps == 9 ? R + 1 : (K.Kc >= 5 ? 3 : 2)); --ring) {
       int pf = ring - R - 1;          // one slot of slack so producers never wait on the tile they just fed
       if (pf > 3) pf = 3;
       if (pf < 1) pf = 1;
@@ -665,6 +671,14 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
     }
   }
   if (!found) return 1;
+  // thin A, wide N (1x1 expand convs and their mirror images in the backward pass): three producer warps keep the
+  // ring full (<= 8 chunks of 16 B per thread and slot) and a third epilogue group takes a third of the columns
+  K.prod_warps = 7;
+  if (K.taps == 1 && !has_z && K.lines * K.CW <= 96 * 8 && K.Ncta >= 48) K.prod_warps = 3;
+  {
+    const char* e = getenv("S2LC_SCONV_PROD");   // A/B hook for the profiles: force 7 producer warps
+    if (e && e[0] == '7') K.prod_warps = 7;
+  }
   K.nacc = 512 / K.Ncta;
   if (K.nacc > SC_MAX_ACC) K.nacc = SC_MAX_ACC;
   if (K.nacc == 3) K.nacc = 2;
@@ -699,7 +713,11 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
       K.koff_b[K.KS] = (uint32_t)((kc * K.Ncta * 128 + k4 * 32) >> 4);
     }
   }
-  const size_t smem = (size_t)fixed + K.w_bytes + (size_t)K.ring * K.slot_bytes + (size_t)(K.pf + 1) * K.zslot_bytes;
+  size_t smem = (size_t)fixed + K.w_bytes + (size_t)K.ring * K.slot_bytes + (size_t)(K.pf + 1) * K.zslot_bytes;
+  if (K.prod_warps == 3) {                       // third statistics area
+    if (smem + 2 * 256 * 4 > (size_t)budget) K.prod_warps = 7;
+    else smem += 2 * 256 * 4;
+  }
   const bool regstat = K.Ncta <= 32;
   void (*kern)(ConvArgs, SPlan) =
       K.taps == 9 ? (regstat ? sconv_kernel<9, true> : sconv_kernel<9, false>)
