@@ -674,7 +674,7 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
   // thin A, wide N (1x1 expand convs and their mirror images in the backward pass): three producer warps keep the
   // ring full (<= 8 chunks of 16 B per thread and slot) and a third epilogue group takes a third of the columns
   K.prod_warps = 7;
-  if (K.taps == 1 && !has_z && K.lines * K.CW <= 96 * 8 && K.Ncta >= 48) K.prod_warps = 3;
+  if (K.taps == 1 && K.lines * K.CW * (has_z ? 2 : 1) <= 96 * 11 && K.Ncta >= 48) K.prod_warps = 3;
   {
     const char* e = getenv("S2LC_SCONV_PROD");   // A/B hook for the profiles: force 7 producer warps
     if (e && e[0] == '7') K.prod_warps = 7;
