@@ -52,7 +52,7 @@ struct SPlan {
   int slot_bytes;    // Kc * chunk_stride
   int zslot_bytes;   // linear staging of z (BatchNorm-backward operand), 0 if unused
   int ring, pf;      // ring slots, prefetch distance (pf < ring - (3x3 ? 2 : 0))
-  int prod_warps;    // producer warps: 7 (two epilogue groups) or 3 (three epilogue groups, thin A / wide N)
+  int prod_warps;    // producer warps: 7 (two epilogue groups), 3 (three groups, thin A / wide N) or 11 (one group)
   int nsplit;        // CTAs sharing a unit along N
   int Ncta;          // output channels per CTA (multiple of 16)
   int nacc;          // TMEM accumulators
@@ -675,6 +675,9 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
   // ring full (<= 8 chunks of 16 B per thread and slot) and a third epilogue group takes a third of the columns
   K.prod_warps = 7;
   if (K.taps == 1 && K.lines * K.CW * (has_z ? 2 : 1) <= 96 * 11 && K.Ncta >= 48) K.prod_warps = 3;
+  // wide A, narrow N (1x1 project convs behind SE gate + SiLU, expand-conv data gradients with the BatchNorm-backward
+  // operand): the transform is the long pole and one epilogue group drains <= 4 column chunks per tile
+  else if (K.taps == 1 && K.Ncta > 32 && K.Ncta <= 64 && K.CW * (has_z ? 2 : 1) >= 24) K.prod_warps = 11;
   {
     const char* e = getenv("S2LC_SCONV_PROD");   // A/B hook for the profiles: force 7 producer warps
     if (e && e[0] == '7') K.prod_warps = 7;
