@@ -516,7 +516,12 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     K.m_on_g = 1; K.n_mtiles = 1; K.nacc = 9;
     // strip width = pixels per ring slot: the widest of 128 / 64 / 32 that divides W and whose rings fit shared memory
     bool ok = false;
-    for (int L = 128; L >= 32 && !ok; L >>= 1) {
+    int Lmax = 128;
+    {
+      const char* e = getenv("S2LC_SWGRAD_LMAX");   // profiling hook: cap the strip width (64 or 32)
+      if (e && (atoi(e) == 64 || atoi(e) == 32)) Lmax = atoi(e);
+    }
+    for (int L = Lmax; L >= 32 && !ok; L >>= 1) {
       if (A.W % L != 0) continue;
       K.lines = L; K.a_lines = L + 2;
       K.a_slot = sw_up((L + 2) * 128, 1024);                        // one 64-channel chunk (nt <= 48)
