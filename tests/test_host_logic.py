@@ -220,3 +220,43 @@ def test_rank_batches_partition_the_tiles(n_tiles, batch, world):
             seen.extend(range(s, e))
     assert sorted(seen) == list(range(n_tiles))
     assert max(per_rank) - min(per_rank) <= 1
+
+
+def _mosaic_worker(rank: int, world: int, port: int, ret) -> None:
+    import numpy as np
+    from oracle.mosaic_oracle import write_tile
+    from s2lc_b200.inference import plan_mosaic, rank_batches
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        h, w, tile, margin, batch = 150, 200, 96, 16, 4
+        origins = plan_mosaic(h, w, tile, margin)
+
+        def tile_logits(i):                     # class (i % 5) + 1 everywhere: which tile wrote a pixel stays visible
+            lg = np.zeros((7, tile, tile), dtype=np.float32)
+            lg[i % 5 + 1] = 1.0
+            return lg
+
+        full = np.zeros((h, w), dtype=np.uint8)
+        for i, (t, l) in enumerate(origins.tolist()):
+            write_tile(full, tile_logits(i), t, l, margin)
+        mine = np.zeros((h, w), dtype=np.uint8)
+        for s, e in rank_batches(origins.shape[0], batch, rank, world):
+            for i in range(s, e):
+                t, l = origins[i].tolist()
+                write_tile(mine, tile_logits(i), t, l, margin)
+        mosaic = torch.from_numpy(mine)
+        dist.all_reduce(mosaic, op=dist.ReduceOp.SUM)     # what MosaicPredictor.predict does with the per-rank buffers
+        ret[rank] = bool(np.array_equal(mosaic.numpy(), full)) and bool((full > 0).all())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_mosaic_assembly_gloo():
+    """Mosaic inference at world_size 2 over gloo: batches of tiles dealt round-robin to the ranks
+    fill disjoint parts of zero-initialised uint8 buffers, so one SUM all-reduce assembles the scene on every rank."""
+    world, port = 2, _free_port()
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_mosaic_worker, args=(world, port, ret), nprocs=world, join=True)
+        assert len(ret) == world and all(ret.values()), dict(ret)
