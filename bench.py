@@ -44,9 +44,18 @@ def parse():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--mode", default="train", choices=["train", "infer"],
+                    help="train: BASELINE.json configs[1-3] (the headline); infer: configs[4], forward-only mosaic predict")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true")
     ap.add_argument("--no-breakdown", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.mode == "infer":
+        if a.batch == 32:
+            a.batch = 256          # configs[4]: bs = 256 tiles per predict call
+        if a.steps == 10:
+            a.steps = 0            # 0 = every strip of the 12.4k-tile mosaic that falls on this rank
+    return a
 
 
 def peaks() -> tuple[dict, str]:
@@ -132,7 +141,10 @@ def run_reference(a) -> None:
     except AttributeError:
         ncpu = os.cpu_count() or 1
     torch.set_num_threads(max(ncpu, 1))
-    step = cpu_reference_step_fn(a.version, a.size, bs)
+    infer = a.mode == "infer"
+    if infer and a.steps <= 0:
+        a.steps = 4
+    step = cpu_eval_step_fn(a.version, a.size, bs) if infer else cpu_reference_step_fn(a.version, a.size, bs)
     for _ in range(max(a.warmup, 1)):
         step()
     t0 = time.perf_counter()
@@ -141,12 +153,13 @@ def run_reference(a) -> None:
     dt = (time.perf_counter() - t0) / a.steps
     v = bs / dt
     cores = torch.get_num_threads()
-    sample = f"{a.steps} steps of 1 tile {a.size}x{a.size} fp32 fwd+focal+bwd+Adam (oracle port of the reference modules)"
+    what = "eval forward + argmax" if infer else "fwd+focal+bwd+Adam"
+    sample = f"{a.steps} steps of 1 tile {a.size}x{a.size} fp32 {what} (oracle port of the reference modules)"
     emit({
-        "impl": "reference", "metric": "train_tiles_per_s", "value": v, "unit": "tiles/s", "n_gpus": a.gpus,
+        "impl": "reference", "metric": "infer_tiles_per_s" if infer else "train_tiles_per_s", "value": v, "unit": "tiles/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"efficientnet-unet-{a.version} fwd+bwd+Adam, focal loss, {a.size}x{a.size} 6-band tiles",
+        "config": {"workload": f"efficientnet-unet-{a.version} {what}, focal loss, {a.size}x{a.size} 6-band tiles",
                    "tier": "B (generalised skip rule, SURVEY.md F1)", "batch_per_step": bs, "host_threads": cores,
                    "os_cpu_count": os.cpu_count(), "torch": torch.__version__},
         "cpu_baseline": {"value": v, "unit": "tiles/s", "cores": cores, "kind": "port", "sample": sample},
@@ -154,10 +167,272 @@ def run_reference(a) -> None:
     })
 
 
+
+def gpu_eager_step_fn(version: str, size: int, batch: int, train: bool = True):
+    """The reference's own GPU path on THIS box: its PyTorch modules (oracle port, same ATen /
+    cuDNN calls) in channels_last under torch.autocast(bf16) — what Lightning's precision="bf16" runs
+    (src/configs/segmentation.py:153) — fwd + focal loss + bwd + torch.optim.Adam (train) or eval forward (infer)."""
+    from oracle import unet_oracle as O
+    from s2lc_b200 import synthetic
+    from s2lc_b200.efficientnet_unet import EfficientNetConfig, EfficientnetUnet
+    torch.backends.cudnn.benchmark = True
+    cfg = EfficientNetConfig(version=version, in_channels=6, num_classes=4, drop_connect_rate=None,
+                             class_distribution=list(synthetic.CLASS_DISTRIBUTION))
+    shapes = {k: tuple(v.shape) for k, v in EfficientnetUnet(cfg).state_dict().items()}
+    sd = synthetic.state_dict_like(shapes, seed=0)
+    state = {}
+    for k, v in sd.items():
+        v = v.cuda()
+        state[k] = v.contiguous(memory_format=torch.channels_last) if v.dim() == 4 else v
+    keys = O.used_param_keys(state)
+    x = synthetic.tiles(batch, size).cuda().contiguous(memory_format=torch.channels_last)
+    y = synthetic.labels(batch, size).cuda()
+    alpha = O.loss_class_weights(list(synthetic.CLASS_DISTRIBUTION), masked_loss=True).cuda()
+    nb = len(O.blocks_for(version)[1])
+    if not train:
+        def step():
+            with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+                return O.unet_forward(state, x, version, training=False).argmax(1)
+        return step
+    for k in keys:
+        state[k] = state[k].clone().requires_grad_(True)
+    opt = torch.optim.Adam([state[k] for k in keys], lr=1.5e-6, weight_decay=0.05)
+    g = torch.Generator(device="cuda").manual_seed(1)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        # drop-connect as the reference draws it (efficientnet_unet.py:257, :390-398): rate 0.2*i/n per block
+        keep = 1.0 - 0.2 * torch.arange(nb, device="cuda", dtype=torch.float32) / nb
+        binary = torch.floor(keep[:, None] + torch.rand(nb, batch, device="cuda", generator=g))
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            logits = O.unet_forward(state, x, version, training=True, update_buffers=True, dc_masks=(binary, keep))
+            loss = O.focal_loss(logits, y, alpha, 2.0, 0.0, 0)
+        loss.backward()
+        opt.step()
+        return loss
+
+    return step
+
+
+def gpu_eager_baseline(a, train: bool = True, batch: int | None = None) -> dict:
+    """Timed in the same process AFTER the main arm (whose memory has been released); CUDA events, 3 warm-up + 5."""
+    batch = batch or a.batch
+    torch.cuda.empty_cache()
+    try:
+        step = gpu_eager_step_fn(a.version, a.size, batch, train)
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 5
+        e0.record()
+        for _ in range(n):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n
+        peak_gb = torch.cuda.max_memory_allocated() / 2 ** 30
+    except torch.OutOfMemoryError as e:        # noqa: F841
+        torch.cuda.empty_cache()
+        if batch > 8:
+            return gpu_eager_baseline(a, train, batch // 2)
+        return {"unavailable": "out of memory"}
+    finally:
+        torch.backends.cudnn.benchmark = False
+    return {"value": batch / (ms / 1e3), "unit": "tiles/s", "ms_per_step": ms, "batch": batch,
+            "what": ("reference modules (oracle port: the same F.conv2d / F.batch_norm / F.silu ... calls) eager on this "
+                     "GPU: cuDNN/ATen, channels_last, torch.autocast(bf16), cudnn.benchmark, "
+                     + ("fwd + focal loss + bwd + torch.optim.Adam, drop-connect 0.2" if train else "eval forward + argmax")),
+            "torch": torch.__version__, "peak_mem_gb": round(peak_gb, 1)}
+
+
+def dp_check(trainer, model, x, y, world: int) -> dict:
+    """SURVEY.md §8(e) on NCCL: the bucket-reduced gradient buffer of an OVERLAPPED step equals the mean of the ranks'
+    local gradients (<= 1e-6), every bucket fired only after its last gradient kernel (local snapshot at fire time ==
+    a separate, non-overlapped backward up to atomics noise), and the parameters are bit-identical on all ranks."""
+    eng = model.engine()
+    fg = eng.flat_grad
+    # (1) non-overlapped local gradient of this rank (same drop-connect draw: rewind the generator's step counter)
+    hook, eng.bucket_hook = eng.bucket_hook, None
+    dc_step = model._dc_step
+    trainer.forward_backward(x, y)
+    torch.cuda.synchronize()
+    local_ref = fg.clone()
+    # (2) overlapped step; each bucket is snapshotted on the comm stream right before its all-reduce
+    eng.bucket_hook = hook
+    model._dc_step = dc_step
+    snap = torch.zeros_like(fg)
+    trainer.snapshot = snap
+    trainer.forward_backward(x, y)
+    torch.cuda.current_stream().wait_stream(trainer.comm_stream)
+    torch.cuda.synchronize()
+    trainer.snapshot = None
+    gathered = [torch.empty_like(snap) for _ in range(world)]
+    dist.all_gather(gathered, snap)
+    mean = torch.stack(gathered).double().mean(0)
+    num = (fg.double() - mean).norm()
+    err_mean = float(num / mean.norm().clamp_min(1e-30))
+    worst_bucket = 0.0
+    for a0, b0, _ in trainer.buckets:
+        den = float(local_ref[a0:b0].double().norm())
+        if den > 0:
+            worst_bucket = max(worst_bucket, float((snap[a0:b0].double() - local_ref[a0:b0].double()).norm()) / den)
+    t = torch.tensor([err_mean, worst_bucket], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    # (3) parameter hash after the timed steps: exact integer sum of the raw bits
+    bits = trainer.optimizer.flat_param.view(torch.int32).to(torch.int64)
+    h = torch.stack([bits.sum(), (bits * (torch.arange(bits.numel(), device="cuda") % 8191 + 1)).sum()])
+    hs = [torch.empty_like(h) for _ in range(world)]
+    dist.all_gather(hs, h)
+    same = all(torch.equal(hs[0], o) for o in hs)
+    return {"ranks": world, "grad_vs_mean_of_rank_grads_rel_err": float(t[0]), "tolerance": 1e-6,
+            "bucket_snapshot_vs_separate_backward_max_rel_err": float(t[1]),
+            "snapshot_note": "two backward passes differ by fp32-atomics order only (<< 1e-2); a bucket fired before "
+                             "its last gradient kernel would be O(1)",
+            "param_hash_equal_all_ranks": bool(same), "buckets": len(trainer.buckets),
+            "ok": bool(float(t[0]) <= 1e-6 and float(t[1]) <= 1e-2 and same)}
+
+
+def run_infer(a) -> None:
+    """BASELINE.json configs[4]: b5 forward-only, bs = 256 tiles per predict call, over a synthetic country-scale
+    mosaic: 49 scene strips of 2 x 128 tiles of 512 x 512 px (12 544 tiles >= AOI `fr`, src/configs/data_config.py:65)
+    dealt round-robin over the ranks.  A step = one strip through MosaicPredictor.predict: int16 scene strip ->
+    tiles (gather + Normalize) -> eval forward -> argmax -> uint8 mosaic strip
+    (src/train_segmentation.py:106-107,135-136; src/experiments/inference_demo.py:14-41)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import numpy as np
+    import s2lc_b200  # noqa: F401
+    from s2lc_b200 import synthetic
+    from s2lc_b200.efficientnet_unet import EfficientNetConfig, EfficientnetUnet
+    from s2lc_b200.inference import MosaicPredictor
+    cfg = EfficientNetConfig(version=a.version, in_channels=6, num_classes=4,
+                             class_distribution=list(synthetic.CLASS_DISTRIBUTION))
+    model = EfficientnetUnet(cfg)
+    model.load_state_dict(synthetic.state_dict_like({k: tuple(v.shape) for k, v in model.state_dict().items()}, seed=0))
+    model = model.cuda().eval().set_precision(a.precision)
+    tile, cols = a.size, 128
+    rows_per_strip = a.batch // cols if a.batch % cols == 0 and a.batch >= cols else 1
+    if rows_per_strip == 1:
+        cols = a.batch
+    total_strips = -(-12400 // a.batch)
+    mine = [s for s in range(total_strips) if s % world == rank]
+    steps = a.steps if a.steps > 0 else len(mine)
+    mean = np.array([5.1, 4.2, 3.9, 9.8, 7.7, 6.0], dtype=np.float32)
+    std = np.array([2.0, 1.7, 1.9, 3.1, 2.6, 2.2], dtype=np.float32)
+    mp = MosaicPredictor(model, mean, std, tile=tile, margin=0, batch=a.batch, rank=0, world_size=1)
+    rs = np.random.RandomState(99 + rank)
+    hs, ws_ = rows_per_strip * tile, cols * tile
+    strip_h = torch.from_numpy(rs.randint(0, 2600, size=(6, hs, ws_), dtype=np.int16)).pin_memory()
+    out_h = torch.empty(hs, ws_, dtype=torch.uint8).pin_memory()
+    strip_d = strip_h.cuda()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 1)):
+        m = mp.predict(strip_d, reduce=False)
+    torch.cuda.synchronize()
+    eng = model.engine()
+    ws = next(w for pool in eng.workspaces.values() for w in pool)
+    agg, top = None, None
+    if not a.no_breakdown:
+        ev = []
+        with torch.no_grad():
+            ws.run_forward(mp.gather(strip_d, mp_origins(mp, hs, ws_)[:ws.N].cuda()), events=ev)
+        torch.cuda.synchronize()
+        agg = {}
+        for e0, e1, i in ev:
+            label, nbytes, flops, _ = ws.fwd_meta[i]
+            r = agg.setdefault(label, [0, 0.0, 0.0, 0.0])
+            r[0] += 1; r[1] += e0.elapsed_time(e1); r[2] += nbytes; r[3] += flops
+        top = max(agg.items(), key=lambda kv: kv[1][1])[0]
+        eng.timing_hook = {"fwd": [], "bwd": [], "only": {top}}
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        m = mp.predict(strip_d, reduce=False)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / steps
+    clocks = sampler.stop() if rank == 0 else None
+    hook, eng.timing_hook = eng.timing_hook, None
+    # ---- end to end: host int16 strip in, host uint8 mosaic strip out, every step (next strip's copy overlaps)
+    copy_stream = torch.cuda.Stream()
+    bufs = [strip_d, torch.empty_like(strip_d)]
+    barrier()
+    t0 = time.perf_counter()
+    with torch.cuda.stream(copy_stream):
+        bufs[0].copy_(strip_h, non_blocking=True)
+    for i in range(steps):
+        cur, nxt = bufs[i % 2], bufs[(i + 1) % 2]
+        torch.cuda.current_stream().wait_stream(copy_stream)
+        with torch.cuda.stream(copy_stream):
+            nxt.copy_(strip_h, non_blocking=True)
+        m = mp.predict(cur, reduce=False)
+        out_h.copy_(m, non_blocking=True)
+        torch.cuda.synchronize()
+    ms_e2e = (time.perf_counter() - t0) * 1e3 / steps
+    barrier()
+    t = torch.tensor([ms, ms_e2e], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    out = None
+    if rank == 0:
+        pk, pk_kind = peaks()
+        out = {
+            "metric": "infer_tiles_per_s", "value": a.batch * world / (ms / 1e3), "unit": "tiles/s", "n_gpus": world,
+            "steps": steps, "warmup": max(a.warmup, 1), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": a.precision.replace("fp32", "f32"), "data": "synthetic",
+            "config": {"workload": f"efficientnet-unet-{a.version} forward-only mosaic predict (gather+Normalize -> eval "
+                                   f"forward -> argmax -> uint8 mosaic), bs={a.batch} tiles/call, {tile}x{tile} 6-band "
+                                   f"tiles, {total_strips * a.batch} tiles = {total_strips} strips dealt over {world} rank(s)",
+                       "tier": "B (generalised skip rule, SURVEY.md F1)", "engine_chunk": mp.engine_batch,
+                       "parallelism": f"dp{world} (tiles strided over ranks, no exchange)",
+                       "l2_policy": "working set >> L2 (805 MB scene strip + GBs of activations per call)"},
+            "e2e": {"value": a.batch * world / (ms_e2e / 1e3), "unit": "tiles/s",
+                    "h2d_bytes_per_step": strip_h.numel() * 2, "d2h_bytes_per_step": out_h.numel()},
+            "gpu_launches": (len(ws.fwd_list) * (a.batch // ws.N) + 2 * (a.batch // ws.N)) * steps,
+            "clocks": clocks, "simt_fallbacks": int(eng.lib.s2lc_simt_fallbacks(0)),
+        }
+        if agg is not None:
+            out["roofline"] = roofline_of(top, ws, hook["fwd"], [], steps * (a.batch // ws.N), pk, pk_kind, ms / (a.batch // ws.N))
+            out["kernel_breakdown"] = breakdown_table(agg)
+    if world == 1 and rank == 0:
+        del mp, model, eng, ws
+        if not a.no_gpu_baseline:
+            out["gpu_eager_baseline"] = gpu_eager_baseline(a, train=False, batch=min(a.batch, 64))
+        if not a.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(a, train=False)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        emit(out)
+
+
+def mp_origins(mp, h, w):
+    from s2lc_b200.inference import plan_mosaic
+    return plan_mosaic(h, w, mp.tile, mp.margin)
+
 def main() -> None:
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+        return
+    if a.mode == "infer":
+        run_infer(a)
         return
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -239,10 +514,11 @@ def main() -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
 
+    dpc = dp_check(trainer, model, x, y, world) if world > 1 else None
     out = None
     if rank == 0:
         pk, pk_kind = peaks()
-        launches = len(ws.fwd_list) + len(ws.bwd_list) + len(eng.packs.get(ws.dtype, {})) + 3
+        launches = len(ws.fwd_list) + len(ws.bwd_list) + 4    # + loss, loss-scale, 2 memsets-as-kernels, Adam+re-pack
         out = {
             "metric": "train_tiles_per_s", "value": a.batch * world / (ms / 1e3), "unit": "tiles/s", "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -255,12 +531,20 @@ def main() -> None:
             "e2e": {"value": a.batch * world / (ms_e2e / 1e3), "unit": "tiles/s",
                     "h2d_bytes_per_step": xh.numel() * 4 + yh.numel() * 8, "d2h_bytes_per_step": 4},
             "gpu_launches": launches * a.steps,
-            "clocks": clocks,
+            "clocks": clocks, "simt_fallbacks": int(eng.lib.s2lc_simt_fallbacks(0)),
         }
+        if dpc is not None:
+            out["dp_check"] = dpc
         if agg is not None:
             out["roofline"] = roofline_of(top, ws, hook["fwd"], hook["bwd"], a.steps, pk, pk_kind, ms)
             out["kernel_breakdown"] = breakdown_table(agg)
-        if world == 1 and not a.no_cpu_baseline:
+    if world == 1 and rank == 0:
+        del trainer, model, eng, ws, bufs, x, y          # release the engine's HBM before the eager comparator
+        if not a.no_gpu_baseline:
+            out["gpu_eager_baseline"] = gpu_eager_baseline(a, train=True)
+            if "value" in out["gpu_eager_baseline"]:
+                out["gpu_eager_baseline"]["ours_over_it"] = round(out["value"] / out["gpu_eager_baseline"]["value"], 3)
+        if not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(a)
     if world > 1:
         dist.barrier()
@@ -348,16 +632,36 @@ def roofline_of(label: str, ws, events_f: list, events_b: list, steps: int, pk: 
     return roof
 
 
-def cpu_baseline(a) -> dict:
-    step = cpu_reference_step_fn(a.version, a.size, 1)
+def cpu_eval_step_fn(version: str, size: int, batch: int):
+    """The reference's CPU predict path (predict_step -> logits -> argmax), oracle port, fp32, eval mode."""
+    import s2lc_b200  # noqa: F401
+    from oracle import unet_oracle as O
+    from s2lc_b200 import synthetic
+    from s2lc_b200.efficientnet_unet import EfficientNetConfig, EfficientnetUnet
+    cfg = EfficientNetConfig(version=version, in_channels=6, num_classes=4, drop_connect_rate=None,
+                             class_distribution=list(synthetic.CLASS_DISTRIBUTION))
+    shapes = {k: tuple(v.shape) for k, v in EfficientnetUnet(cfg).state_dict().items()}
+    sd = synthetic.state_dict_like(shapes, seed=0)
+    x = synthetic.tiles(batch, size)
+
+    def step():
+        with torch.no_grad():
+            return O.unet_forward(sd, x, version, training=False).argmax(1)
+
+    return step
+
+
+def cpu_baseline(a, train: bool = True) -> dict:
+    step = cpu_reference_step_fn(a.version, a.size, 1) if train else cpu_eval_step_fn(a.version, a.size, 1)
     step()
     t0 = time.perf_counter()
-    n = 2
+    n = 2 if train else 4
     for _ in range(n):
         step()
     dt = (time.perf_counter() - t0) / n
+    what = "fp32, fwd+focal+bwd+Adam" if train else "fp32, eval forward + argmax"
     return {"value": 1.0 / dt, "unit": "tiles/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{n} steps of 1 tile {a.size}x{a.size}, fp32, fwd+focal+bwd+Adam on the host cores "
+            "sample": f"{n} steps of 1 tile {a.size}x{a.size}, {what} on the host cores "
                       f"(os.cpu_count()={os.cpu_count()})"}
 
 

@@ -255,6 +255,34 @@ int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* e
                        float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
                        void* stream);
 
+/* Adam + re-pack of the tensor-core weight operands in ONE pass over the flat parameter buffer (row f1 as SURVEY.md
+ * §8 states it: "fused multi-tensor Adam + bf16 weight re-pack in one pass").  `entries` is a DEVICE table sorted by
+ * `start`; entry e says: the parameter stored at param[start .. start+numel) (reference layout OIHW / IOHW) has a
+ * packed copy dst[Npad, Kpad] (layout of s2lc_weight_pack) whose element (n1*N2 + n2, tap*Cpad + c) is the source
+ * element n1*s1 + n2*s2 + tap*st + c*sc; stride[]/role[] list those four source strides in DESCENDING order with
+ * role 0 = n1, 1 = n2, 2 = tap, 3 = c (stride 0 = extent 1).  Padding of dst is never written (zero from creation). */
+typedef struct {
+  int64_t start, numel;
+  void* dst;
+  int64_t stride[4];
+  int32_t role[4];
+  int32_t N2, Tt, Cpad, Kpad, flip, dtype;
+} s2lc_pack_entry;
+int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+                            const s2lc_pack_entry* entries, int32_t n_entries, void* stream);
+
+/* ---- diagnostics.  s2lc_simt_fallbacks: number of bf16 conv / weight-gradient calls since load that no tcgen05 engine
+ * took and that ran on the CUDA-core verification engine instead (include/s2lc.h top: the product path is tcgen05;
+ * the count must stay 0 on the reference architectures — tests and bench.py assert / report it).  reset = 1 clears. */
+int64_t s2lc_simt_fallbacks(int32_t reset);
+/* SM count of the current device (sizes every persistent grid; read once from the driver, not a constant). */
+int32_t s2lc_num_sms(void);
+/* Test / profiling switches (bit 0: no streaming engines, 1: force the CUDA-core engine, 2: 7 producer warps,
+ * 3: no TMA feed; bits 8-15: strip-width cap of the streaming 3x3 weight gradient).  Returns the previous value.
+ * Initialised once from S2LC_* environment variables; the default 0 is the product path. */
+uint32_t s2lc_set_debug_flags(uint32_t flags);
+
 #ifdef __cplusplus
 }
 #endif

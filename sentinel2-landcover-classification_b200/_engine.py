@@ -36,13 +36,30 @@ class PackedWeight:
     def __init__(self, src: torch.Tensor, dtype: torch.dtype, n1: int, n2: int, taps: int, c: int, s1: int, s2: int,
                  st: int, sc: int, flip: bool = False, cpad: int | None = None) -> None:
         self.src = src
+        self.dtype = dtype
         self.n_out = n1 * n2
         self.npad = _up(self.n_out, 16)
         self.cpad = _up(c, 8) if cpad is None else cpad
         self.kpad = _up(taps * self.cpad, 64)
         self.buf = torch.zeros(self.npad, self.kpad, dtype=dtype, device=src.device)
+        self.geom = (n1, n2, taps, c, s1, s2, st, sc, bool(flip))
         self.args = (src.data_ptr(), self.buf.data_ptr(), _DT[dtype], n1, n2, taps, c, self.npad, self.cpad,
                      self.kpad, s1, s2, st, sc, int(flip))
+
+    def entry(self, flat_base_ptr: int) -> "L.PackEntry":
+        """This pack job as a row of the fused Adam + re-pack table (include/s2lc.h s2lc_pack_entry): source strides
+        in descending order with their roles (0 = n1, 1 = n2, 2 = tap, 3 = c); extent-1 dimensions get stride 0."""
+        n1, n2, taps, c, s1, s2, st, sc, flip = self.geom
+        dims = [(s1 if n1 > 1 else 0, 0), (s2 if n2 > 1 else 0, 1), (st if taps > 1 else 0, 2), (sc if c > 1 else 0, 3)]
+        dims.sort(key=lambda d: -d[0])
+        e = L.PackEntry()
+        off = self.src.data_ptr() - flat_base_ptr
+        assert off >= 0 and off % 4 == 0
+        e.start, e.numel, e.dst = off // 4, self.src.numel(), self.buf.data_ptr()
+        for i, (stride, role) in enumerate(dims):
+            e.stride[i], e.role[i] = stride, role
+        e.N2, e.Tt, e.Cpad, e.Kpad, e.flip, e.dtype = n2, taps, self.cpad, self.kpad, int(flip), _DT[self.dtype]
+        return e
 
 
 class Engine:
@@ -70,9 +87,10 @@ class Engine:
                            for (k, p), o in ((kp, self.grad_offsets[kp[0]]) for kp in self.used)}
         self.workspaces: dict[tuple, list[Workspace]] = {}
         self.packs: dict[torch.dtype, dict[str, PackedWeight]] = {}
-        self._pack_sig: dict[torch.dtype, int] = {}
+        self._pack_sig: dict[torch.dtype, tuple] = {}
         self._param_ptrs = self._ptr_signature()
-        self.weights_dirty = True
+        self.weight_gen = 0        # bumped by every out-of-band parameter update (FusedAdam writes through raw pointers)
+        self.packs_version = 0     # bumped whenever a packed weight is added (FusedAdam rebuilds its table)
         self.direct_grad = False   # DataParallelTrainer: leave grads in flat_grad instead of returning clones
         self.timing_hook = None    # {"fwd": [], "bwd": [], "only": {kernel-class labels}} — see Workspace.run_forward
 
@@ -85,17 +103,23 @@ class Engine:
         if key not in d:
             d[key] = factory()
             self._pack_sig.pop(dtype, None)
+            self.packs_version += 1
         return d[key]
 
+    def weight_signature(self) -> tuple:
+        """(generation of out-of-band updates, sum of autograd versions): changes whenever any parameter changed."""
+        return (self.weight_gen, sum(p._version for _, p in self.used))
+
     def repack(self, dtype: torch.dtype, stream: int) -> None:
-        sig = sum(p._version for _, p in self.used)
-        if not self.weights_dirty and self._pack_sig.get(dtype) == sig:
+        """Refresh the packed copies of ``dtype`` unless they were made from the current parameter values (tracked
+        PER DTYPE: a bf16 forward must not mark stale fp32 copies clean)."""
+        sig = self.weight_signature()
+        if self._pack_sig.get(dtype) == sig:
             return
         fn = self.lib.s2lc_weight_pack
         for pw in self.packs.get(dtype, {}).values():
             L.check(fn(*pw.args, stream))
         self._pack_sig[dtype] = sig
-        self.weights_dirty = False
 
     # ---------------------------------------------------------------- workspaces
     def workspace(self, x: torch.Tensor, dtype: torch.dtype, training: bool, need_grad: bool) -> "Workspace":
@@ -109,10 +133,10 @@ class Engine:
         for ws in pool:
             if not ws.in_flight:
                 return ws
-        if len(pool) >= 2:       # a forward whose backward never ran (e.g. validation under grad mode): recycle
-            ws = pool[0]
-            ws.in_flight = False
-            return ws
+        if len(pool) >= 4:
+            raise RuntimeError(
+                "four forward passes of one shape are waiting for their backward: activations are saved per workspace "
+                "and are not recycled while in flight — call backward() (or run the forward under torch.no_grad())")
         ws = Workspace(self, x.shape[0], x.shape[2], x.shape[3], dtype, training, need_grad)
         pool.append(ws)
         return ws
@@ -143,6 +167,7 @@ class Workspace:
         self.training, self.need_grad = training, need_grad
         self.dev = eng.device
         self.in_flight = False
+        self.lease_id = 0
         self._keep: list = []
         self._tensors: list[torch.Tensor] = []
         self._stats_f: list[int] = []
@@ -788,15 +813,35 @@ class Workspace:
                     hook(b)
 
 
+class _Lease:
+    """Marks a workspace as holding the saved activations of a live autograd graph.  Released by backward(), or when
+    the graph is dropped without a backward (the lease dies with the autograd context), so a training-mode forward
+    whose result is discarded does not pin its workspace."""
+
+    def __init__(self, ws: "Workspace") -> None:
+        self.ws = ws
+        ws.lease_id += 1
+        self.id = ws.lease_id
+        ws.in_flight = True
+
+    def release(self) -> None:
+        if self.ws.lease_id == self.id:
+            self.ws.in_flight = False
+
+    __del__ = release
+
+
 class _UnetFunction(torch.autograd.Function):
     """One autograd node for the whole network: forward = the launch list, backward = its hand-written reverse."""
 
     @staticmethod
     def forward(ctx, model: EfficientnetUnet, ws: Workspace, x: torch.Tensor, *params):
         out = ws.run_forward(x)
-        ws.in_flight = True
+        ctx.lease = _Lease(ws)
         ctx.ws, ctx.model = ws, model
-        return out.clone()
+        # a trainer that owns the loop (direct_grad) consumes the logits before the next forward: hand out the
+        # workspace's own buffer; everyone else gets a private copy, as a fresh tensor from the reference module is
+        return out if ws.eng.direct_grad else out.clone()
 
     @staticmethod
     def backward(ctx, dlogits: torch.Tensor):
@@ -805,8 +850,11 @@ class _UnetFunction(torch.autograd.Function):
         d = dlogits.permute(0, 2, 3, 1)
         if d.dtype != ws.dtype or not d.is_contiguous():
             d = d.to(ws.dtype).contiguous()
+        if not ws.in_flight or ws.lease_id != ctx.lease.id:
+            raise RuntimeError("the activations of this forward pass were overwritten by a later forward (workspace "
+                               "lease lost): backward() must run before the workspace is reused")
         ws.run_backward(d)
-        ws.in_flight = False
+        ctx.lease.release()
         eng = ws.eng
         if eng.direct_grad:
             for k, p in eng.used:                       # parameters see the flat buffer as their .grad

@@ -40,6 +40,11 @@ class ConvParams(C.Structure):
                 ("stats_rowscale", vp)]
 
 
+class PackEntry(C.Structure):
+    _fields_ = [("start", i64), ("numel", i64), ("dst", vp), ("stride", i64 * 4), ("role", i32 * 4), ("N2", i32),
+                ("Tt", i32), ("Cpad", i32), ("Kpad", i32), ("flip", i32), ("dtype", i32)]
+
+
 class WgradParams(C.Structure):
     _fields_ = [("mode", i32), ("dtype", i32), ("N", i32), ("H", i32), ("W", i32), ("Cin", i32), ("Cout", i32),
                 ("_pad", i32), ("a", C.POINTER(Lazy)), ("g", C.POINTER(LazyGrad)), ("dw", vp), ("dbias", vp)]
@@ -87,6 +92,10 @@ _PROTOS = {
     "s2lc_loss_fwd_bwd": ([vp, i64, vp, vp, f32, f32, i64, i32, i32, vp, vp, vp, i64, i64, i32, i32, vp], i32),
     "s2lc_scale_inplace": ([vp, i64, vp, i64, i32, i32, vp], i32),
     "s2lc_adam_step": ([vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, vp], i32),
+    "s2lc_adam_pack_step": ([vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, vp, i32, vp], i32),
+    "s2lc_simt_fallbacks": ([i32], i64),
+    "s2lc_num_sms": ([], i32),
+    "s2lc_set_debug_flags": ([C.c_uint32], C.c_uint32),
 }
 
 EXPORTED_SYMBOLS = tuple(_PROTOS)

@@ -21,7 +21,14 @@ int32_t check_launch(const char* what);
     }                                   \
   } while (0)
 
-constexpr int kNumSMs = 148;
+// SM count of the CURRENT device, read once per device from the driver (sizes every persistent grid; a partitioned or
+// different-SKU part must not silently get B200's 148).  Host side only.
+int num_sms();
+// Test / profiling switches (s2lc_set_debug_flags; initialised ONCE from the environment at first use, never read
+// per launch): the defaults (0) are the product path.
+enum : uint32_t { DBG_NO_STREAM = 1u, DBG_FORCE_SIMT = 2u, DBG_SCONV_PROD7 = 4u, DBG_NO_TMA = 8u };
+uint32_t debug_flags();          // bits above; bits 8-15 = strip-width cap of the streaming 3x3 weight gradient (0 = none)
+#define kNumSMs (::s2lc::num_sms())
 
 // ------------------------------------------------------------------ scalar load/store by storage type
 template <typename T> __device__ __forceinline__ float ldf(const T* p);

@@ -6,14 +6,7 @@
 
 using namespace s2lc;
 
-static bool force_simt() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("S2LC_FORCE_SIMT");
-    v = (e && e[0] == '1') ? 1 : 0;
-  }
-  return v == 1;
-}
+static bool force_simt() { return (debug_flags() & DBG_FORCE_SIMT) != 0; }
 
 extern "C" {
 
@@ -50,6 +43,7 @@ int32_t s2lc_conv_fwd(const s2lc_conv_params* p, void* stream) {
     if (r <= 0) return r;  // taken (0) or error (<0)
     r = launch_conv_tc(A, st);
     if (r <= 0) return r;
+    note_simt_fallback();   // counted, never silent: s2lc_simt_fallbacks() must stay 0 on the reference architectures
   }
   return launch_conv_simt(A, st);
 }
@@ -69,6 +63,7 @@ int32_t s2lc_conv_wgrad(const s2lc_wgrad_params* p, void* stream) {
     if (r <= 0) return r;
     r = launch_wgrad_tc(A, st);
     if (r <= 0) return r;
+    note_simt_fallback();
   }
   return launch_wgrad_simt(A, st);
 }

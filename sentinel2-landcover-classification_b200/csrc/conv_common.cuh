@@ -166,6 +166,7 @@ __device__ __forceinline__ int64_t wgrad_index(const WgradArgs& P, int n, int k)
   return ((int64_t)k * P.Cout + co) * 4 + q;
 }
 
+void note_simt_fallback();
 int32_t launch_conv_simt(const ConvArgs& A, cudaStream_t st);
 int32_t launch_wgrad_simt(const WgradArgs& A, cudaStream_t st);
 int32_t launch_conv_tc(const ConvArgs& A, cudaStream_t st);      // igemm_tc.cu; returns 1 if shape not taken

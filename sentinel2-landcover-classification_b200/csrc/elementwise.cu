@@ -5,6 +5,7 @@
 // vector per thread so per-channel reductions stay in registers until one flush per CTA.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -25,6 +26,37 @@ int32_t check_launch(const char* what) {
   }
   return S2LC_OK;
 }
+
+int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+static uint32_t g_dbg = 0;
+static bool g_dbg_init = false;
+uint32_t debug_flags() {
+  if (!g_dbg_init) {
+    uint32_t f = 0;
+    const char* e;
+    if ((e = getenv("S2LC_NO_STREAM")) && e[0] == '1') f |= DBG_NO_STREAM;
+    if ((e = getenv("S2LC_FORCE_SIMT")) && e[0] == '1') f |= DBG_FORCE_SIMT;
+    if ((e = getenv("S2LC_SCONV_PROD")) && e[0] == '7') f |= DBG_SCONV_PROD7;
+    if ((e = getenv("S2LC_NO_TMA")) && e[0] == '1') f |= DBG_NO_TMA;
+    if ((e = getenv("S2LC_SWGRAD_LMAX")) && (atoi(e) == 64 || atoi(e) == 32)) f |= (uint32_t)atoi(e) << 8;
+    g_dbg = f;
+    g_dbg_init = true;
+  }
+  return g_dbg;
+}
+static long long g_simt_fallbacks = 0;
+void note_simt_fallback() { __atomic_fetch_add(&g_simt_fallbacks, 1, __ATOMIC_RELAXED); }
 
 // Thread layout for [rows, C] tensors processed in 8-channel vectors.
 struct ChanIter {
@@ -224,10 +256,10 @@ template <> struct RawV8<float> {
 template <typename T> struct SeU { static constexpr int value = sizeof(T) == 2 ? 4 : 2; };   // rows in flight
 constexpr int SE_BLOCKS_PER_SM = 4;
 constexpr int SE_APPLY_BLOCKS_PER_SM = 3;   // se_bwd_apply holds 4 per-channel vectors + 2 accumulators: 85 registers
-// pooled[n, c] += (1/HW) * sum_{rows of sample n in this split} act(z*scale+shift)
+// pooled[n, c] = (1/HW) * sum_{rows of sample n} act(z*scale+shift), split over gridDim.x blocks per sample
 template <typename T, bool WITH_DA>
 __global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t ld_da, float* __restrict__ out, int HW,
-                               int C, float mul) {
+                               int C, float mul, float* __restrict__ part, unsigned* __restrict__ counter) {
   // grid: (splits, N).  WITH_DA: out[n,c] += sum da*act(u)  (d gate), else mean of act(u).
   const int CV = C / 8;
   ChanIter it(CV);
@@ -272,20 +304,36 @@ __global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_laz
         }
       }
     }
-    // reduce across the rows_par threads that share a channel vector
+    // DETERMINISTIC reduction (two identical predictions must give identical class maps): the rows_par threads that
+    // share a channel vector are summed in index order through shared memory, ...
     const int nsm = it.cvb * 8;
-    for (int i = threadIdx.x; i < nsm; i += blockDim.x) smem[i] = 0.f;
-    __syncthreads();
-    if (it.active && cv < CV) {
+    if (it.active) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(&smem[it.c_local * 8 + j], acc[j]);
+      for (int j = 0; j < 8; ++j) smem[(it.r_local * it.cvb + it.c_local) * 8 + j] = (cv < CV) ? acc[j] : 0.f;
     }
     __syncthreads();
     for (int i = threadIdx.x; i < nsm; i += blockDim.x) {
+      float t = 0.f;
+      for (int r = 0; r < it.rows_par; ++r) t += smem[r * nsm + i];
       int c = cv0 * 8 + i;
-      if (c < C) atomicAdd(&out[(int64_t)n * C + c], smem[i] * mul);
+      if (c < C) part[((int64_t)n * gridDim.x + blockIdx.x) * C + c] = t;
     }
     __syncthreads();
+  }
+  // ... and the per-block partials of a sample by the LAST block to finish, again in index order.
+  __shared__ unsigned ticket;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) ticket = atomicAdd(&counter[n], 1u);
+  __syncthreads();
+  if (ticket == gridDim.x - 1) {
+    __threadfence();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      float t = 0.f;
+      for (int sidx = 0; sidx < (int)gridDim.x; ++sidx) t += __ldcg(&part[((int64_t)n * gridDim.x + sidx) * C + c]);
+      out[(int64_t)n * C + c] = t * mul;
+    }
+    if (threadIdx.x == 0) counter[n] = 0u;    // ready for the next launch on this stream
   }
 }
 
@@ -658,6 +706,58 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
 }
 
+// Adam + bf16/fp32 GEMM-operand re-pack in ONE pass over the flat parameter buffer.  `ent` is a table
+// of pack jobs sorted by `start` (flat offset of the source parameter); a parameter with a forward and a data-gradient
+// operand has two consecutive entries with the same start.  Each thread updates its elements and scatters the new value
+// to every packed copy: source offset -> (n1, n2, tap, c) by peeling the source strides in descending order.
+__device__ __forceinline__ void pack_scatter(const s2lc_pack_entry& e, int64_t r, float val) {
+  int idx[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int d = 0; d < 4; ++d) {
+    const int64_t s = e.stride[d];
+    if (s > 0) {
+      const int64_t q = r / s;
+      idx[e.role[d]] = (int)q;
+      r -= q * s;
+    }
+  }
+  const int n = idx[0] * e.N2 + idx[1];
+  const int tap = e.flip ? (e.Tt - 1 - idx[2]) : idx[2];
+  const int64_t di = (int64_t)n * e.Kpad + (int64_t)tap * e.Cpad + idx[3];
+  if (e.dtype == S2LC_BF16) reinterpret_cast<bf16*>(e.dst)[di] = __float2bfloat16_rn(val);
+  else reinterpret_cast<float*>(e.dst)[di] = val;
+}
+
+__global__ void __launch_bounds__(256) adam_pack_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                        float* __restrict__ m, float* __restrict__ v, int64_t n,
+                                                        float lr, float b1, float b2, float eps, float wd, float bc1,
+                                                        float bc2_sqrt, float gscale,
+                                                        const s2lc_pack_entry* __restrict__ ent, int n_ent) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float pi = p[i];
+    float gi = g[i] * gscale + wd * pi;
+    float mi = b1 * m[i] + (1.f - b1) * gi;
+    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    float denom = sqrtf(vi) / bc2_sqrt + eps;
+    pi = pi - (lr / bc1) * (mi / denom);
+    p[i] = pi;
+    // last entry with start <= i
+    int lo = 0, hi = n_ent;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (ent[mid].start <= i) lo = mid + 1; else hi = mid;
+    }
+    for (int j = lo - 1; j >= 0; --j) {
+      const s2lc_pack_entry& e = ent[j];
+      if (i >= e.start + e.numel) break;          // entries with one start are contiguous; sources never overlap
+      pack_scatter(e, i - e.start, pi);
+      if (j > 0 && ent[j - 1].start != e.start) break;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ lazy gradient -> tensor
 // g = p*dy*rowscale + q*z + t written out once (in place over dy is allowed).  Used in front of the compute-heavy
 // decoder 3x3 layers: their weight- and data-gradient engines split the channels over many CTAs, each of which would
@@ -842,23 +942,53 @@ static inline int se_splits(int N, int HW, int C, int blocks_per_sm = SE_BLOCKS_
   return s < 1 ? 1 : s;
 }
 
+// Library-owned scratch of the deterministic squeeze-excite reductions: per-block partials [N][splits][C] and one
+// arrival counter per sample (zero between launches).  Cached per device, grown on demand (include/s2lc.h: "the
+// library never allocates persistent device memory except a cached, size-keyed workspace pool").  One stream per
+// process launches these kernels, so consecutive launches reuse the buffer in stream order.
+struct SeScratch { float* part = nullptr; size_t floats = 0; unsigned* counter = nullptr; int n = 0; };
+static SeScratch g_se[64];
+static int32_t se_scratch(int N, size_t floats, float** part, unsigned** counter) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("se scratch: bad device"); return S2LC_ERR_CUDA; }
+  SeScratch& sc = g_se[dev];
+  if (floats > sc.floats) {
+    if (sc.part) cudaFree(sc.part);
+    sc.floats = floats + floats / 2;
+    if (cudaMalloc(&sc.part, sc.floats * sizeof(float)) != cudaSuccess) { sc.part = nullptr; sc.floats = 0; set_error("se scratch: cudaMalloc"); return S2LC_ERR_CUDA; }
+  }
+  if (N > sc.n) {
+    if (sc.counter) cudaFree(sc.counter);
+    sc.n = N < 1024 ? 1024 : 2 * N;
+    if (cudaMalloc(&sc.counter, sc.n * sizeof(unsigned)) != cudaSuccess || cudaMemset(sc.counter, 0, sc.n * sizeof(unsigned)) != cudaSuccess) {
+      sc.counter = nullptr; sc.n = 0; set_error("se scratch: cudaMalloc"); return S2LC_ERR_CUDA;
+    }
+  }
+  *part = sc.part; *counter = sc.counter;
+  return S2LC_OK;
+}
+
 int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, int32_t C, int32_t dtype,
                      void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0, S2LC_ERR_ALIGN, "se_pool: alignment (C=%d)", C);
-  cudaMemsetAsync(pooled, 0, sizeof(float) * (size_t)N * C, (cudaStream_t)stream);
   dim3 grid(se_splits(N, HW, C), N);
-  DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, 256, stats_smem(C, 1), (cudaStream_t)stream>>>(
-                        *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW)));
+  float* part; unsigned* counter;
+  int32_t rc = se_scratch(N, (size_t)N * grid.x * C, &part, &counter);
+  if (rc) return rc;
+  DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, 256, 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
+                        *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW, part, counter)));
   return check_launch("se_pool");
 }
 
 int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, float* dgate, int32_t N, int32_t HW,
                            int32_t C, int32_t dtype, void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_da % 8 == 0, S2LC_ERR_ALIGN, "se_bwd_reduce: alignment (C=%d)", C);
-  cudaMemsetAsync(dgate, 0, sizeof(float) * (size_t)N * C, (cudaStream_t)stream);
   dim3 grid(se_splits(N, HW, C), N);
-  DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, 256, stats_smem(C, 1), (cudaStream_t)stream>>>(
-                        *in, (const T*)da, ld_da, dgate, HW, C, 1.f)));
+  float* part; unsigned* counter;
+  int32_t rc = se_scratch(N, (size_t)N * grid.x * C, &part, &counter);
+  if (rc) return rc;
+  DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, 256, 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
+                        *in, (const T*)da, ld_da, dgate, HW, C, 1.f, part, counter)));
   return check_launch("se_bwd_reduce");
 }
 
@@ -979,6 +1109,31 @@ int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* e
                                                                       beta2, eps, weight_decay, (float)bc1,
                                                                       (float)sqrt(bc2), grad_scale);
   return check_launch("adam_step");
+}
+
+int64_t s2lc_simt_fallbacks(int32_t reset) {
+  long long v = __atomic_load_n(&s2lc::g_simt_fallbacks, __ATOMIC_RELAXED);
+  if (reset) __atomic_store_n(&s2lc::g_simt_fallbacks, 0, __ATOMIC_RELAXED);
+  return (int64_t)v;
+}
+int32_t s2lc_num_sms(void) { return s2lc::num_sms(); }
+uint32_t s2lc_set_debug_flags(uint32_t flags) {
+  uint32_t old = s2lc::debug_flags();
+  s2lc::g_dbg = flags;
+  return old;
+}
+
+int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+                            const s2lc_pack_entry* entries, int32_t n_entries, void* stream) {
+  S2LC_REQUIRE(n_entries == 0 || entries != nullptr, S2LC_ERR_SHAPE, "adam_pack_step: null entry table");
+  double bc1 = 1.0 - pow((double)beta1, (double)step);
+  double bc2 = 1.0 - pow((double)beta2, (double)step);
+  adam_pack_kernel<<<grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr,
+                                                                           beta1, beta2, eps, weight_decay, (float)bc1,
+                                                                           (float)sqrt(bc2), grad_scale, entries,
+                                                                           n_entries);
+  return check_launch("adam_pack_step");
 }
 
 }  // extern "C"

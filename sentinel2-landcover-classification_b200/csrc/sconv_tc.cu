@@ -612,10 +612,7 @@ static int sc_up(int x, int m) { return (x + m - 1) / m * m; }
 
 // Returns 0 if launched, <0 on error, 1 if this shape is left to the tile-at-a-time engine (igemm_tc.cu).
 int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
-  {
-    const char* e = getenv("S2LC_NO_STREAM");   // test hook: compare against the tile-at-a-time engine
-    if (e && e[0] == '1') return 1;
-  }
+  if (debug_flags() & DBG_NO_STREAM) return 1;   // test hook: compare against the tile-at-a-time engine
   if (A.dtype != S2LC_BF16 || (A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONV_1X1)) return 1;
   if (A.C % 8 != 0 || A.Kpad % 64 != 0 || !sc_aligned16(A.w_packed)) return 1;
   if (A.a_is_grad) {
@@ -678,10 +675,7 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
   // wide A, narrow N (1x1 project convs behind SE gate + SiLU, expand-conv data gradients with the BatchNorm-backward
   // operand): the transform is the long pole and one epilogue group drains <= 4 column chunks per tile
   else if (K.taps == 1 && K.Ncta > 32 && K.Ncta <= 64 && K.CW * (has_z ? 2 : 1) >= 24) K.prod_warps = 11;
-  {
-    const char* e = getenv("S2LC_SCONV_PROD");   // A/B hook for the profiles: force 7 producer warps
-    if (e && e[0] == '7') K.prod_warps = 7;
-  }
+  if (debug_flags() & DBG_SCONV_PROD7) K.prod_warps = 7;   // A/B hook for the profiles
   K.nacc = 512 / K.Ncta;
   if (K.nacc > SC_MAX_ACC) K.nacc = SC_MAX_ACC;
   if (K.nacc == 3) K.nacc = 2;

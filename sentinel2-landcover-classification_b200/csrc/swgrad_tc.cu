@@ -474,10 +474,7 @@ static int sw_up(int x, int m) { return (x + m - 1) / m * m; }
 
 // Returns 0 if launched, <0 on error, 1 if this shape is left to the slab engine (wgrad_tc.cu).
 int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
-  {
-    const char* e = getenv("S2LC_NO_STREAM");   // test hook: compare against the slab engine
-    if (e && e[0] == '1') return 1;
-  }
+  if (debug_flags() & DBG_NO_STREAM) return 1;   // test hook: compare against the slab engine
   if (A.dtype != S2LC_BF16 || (A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONV_1X1 && A.mode != S2LC_CONVT_FWD)) return 1;
   const int children = A.mode == S2LC_CONVT_FWD ? 4 : 1;
   int lw = 0;
@@ -517,10 +514,7 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     // strip width = pixels per ring slot: the widest of 128 / 64 / 32 that divides W and whose rings fit shared memory
     bool ok = false;
     int Lmax = 128;
-    {
-      const char* e = getenv("S2LC_SWGRAD_LMAX");   // profiling hook: cap the strip width (64 or 32)
-      if (e && (atoi(e) == 64 || atoi(e) == 32)) Lmax = atoi(e);
-    }
+    if ((debug_flags() >> 8) & 0xffu) Lmax = (int)((debug_flags() >> 8) & 0xffu);   // profiling hook: strip-width cap
     for (int L = Lmax; L >= 32 && !ok; L >>= 1) {
       if (A.W % L != 0) continue;
       K.lines = L; K.a_lines = L + 2;

@@ -165,13 +165,32 @@ def _init_like_reference(root: nn.Module) -> None:
             nn.init.zeros_(m.bias)
 
 
+def _init_classification_bias(layer: nn.Conv2d, class_distribution) -> None:
+    """``initialize_classification_layer_bias`` of the reference (src/utils.py:174-188), error behaviour included: a
+    missing distribution raises TypeError (``torch.tensor(None)``), one that does not sum to 1 or has a single class
+    fails the reference's two asserts; two classes -> scalar log-odds of the positive class, otherwise log(p + 1e-6)."""
+    if class_distribution is None:
+        raise TypeError("class_distribution must be a list of class frequencies (the reference's "
+                        "initialize_classification_layer_bias raises on None as well)")
+    dist = torch.tensor(class_distribution, dtype=torch.float32) + 1e-6
+    assert torch.isclose(dist.sum(), torch.tensor(1.0)), f"Must sum to 1, got distribution: {class_distribution}"
+    assert len(class_distribution) > 1, "Class distribution must have at least 2 classes"
+    if len(dist) == 2:
+        layer.bias.data.fill_(float((dist[1] / dist[0]).log()))
+    else:
+        layer.bias.data = dist.log()
+
+
 class EfficientnetUnet(nn.Module):
     """Drop-in for the reference class of the same name (constructor :107, forward :125)."""
 
     def __init__(self, config: EfficientNetConfig, concat_input: bool = True) -> None:
         super().__init__()
         if not concat_input:
-            raise NotImplementedError("concat_input=False is not used anywhere in the reference and is not built")
+            # the reference's own forward fails with concat_input=False: out_conv1x1 is built for size[5] = 32 channels
+            # (efficientnet_unet.py:121) but then receives the 64 channels of double_convs[3] (:133-137)
+            raise NotImplementedError("concat_input=False: the reference's forward raises a channel mismatch at "
+                                      "out_conv1x1 in this mode (64 channels into a 32-channel conv); not built")
         self.config = config
         self.encoder = _EncoderParams(config)
         head_c = _HEAD_CHANNELS[config.version]
@@ -185,12 +204,7 @@ class EfficientnetUnet(nn.Module):
         self.input_double_conv = _double_conv_params(cat[4], 32)
         self.out_conv1x1 = nn.Conv2d(cat[5], config.num_classes, kernel_size=1)
         _init_like_reference(self)
-        if config.class_distribution is not None:  # reference src/utils.py:174-188
-            dist = torch.tensor(config.class_distribution, dtype=torch.float32) + 1e-6
-            if len(dist) == 2:
-                self.out_conv1x1.bias.data.fill_(float((dist[1] / dist[0]).log()))
-            else:
-                self.out_conv1x1.bias.data = dist.log()
+        _init_classification_bias(self.out_conv1x1, config.class_distribution)
         self.precision: str = "auto"       # "auto": bf16 under torch.autocast(bf16) else fp32; or "bf16" / "fp32"
         self._engine = None
         self._dc_masks = None

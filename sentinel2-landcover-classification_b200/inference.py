@@ -57,7 +57,7 @@ class MosaicPredictor:
 
     def __init__(self, model: torch.nn.Module, mean, std, tile: int = 512, margin: int = 0, batch: int = 8,
                  max_pixel_value: float = 255.0, rank: int | None = None, world_size: int | None = None,
-                 device: torch.device | str = "cuda") -> None:
+                 device: torch.device | str = "cuda", engine_batch: int = 64) -> None:
         plan_mosaic(tile, tile, tile, margin)                     # validates tile / margin
         self.model, self.tile, self.margin, self.batch = model, int(tile), int(margin), int(batch)
         self.device = torch.device(device)
@@ -68,6 +68,13 @@ class MosaicPredictor:
         self.rank = rank if rank is not None else (torch.distributed.get_rank() if dist_on else 0)
         self.world_size = world_size if world_size is not None else (torch.distributed.get_world_size() if dist_on else 1)
         self.lib = L.load()
+        # tiles per network launch list: a predict call of ``batch`` tiles (bs = 256 in BASELINE.json configs[4]) runs
+        # as batch / engine_batch forward passes.  Eval mode has no cross-sample arithmetic (running BatchNorm
+        # statistics, per-sample squeeze-excite), so the split is exact; it keeps every activation tensor below
+        # 2^31 elements (256 x 256 x 256 x 144 = 2.4e9 at bs = 256) and the workspace at ~16 GB instead of ~64 GB.
+        self.engine_batch = max(1, min(int(engine_batch), self.batch))
+        while self.batch % self.engine_batch:
+            self.engine_batch -= 1
 
     # ------------------------------------------------------------------ the two device stages around the network
     def gather(self, scene: torch.Tensor, origins: torch.Tensor) -> torch.Tensor:
@@ -113,11 +120,17 @@ class MosaicPredictor:
                     park = origins_d.new_full((self.batch - (e - s), 2), -self.tile)
                     o = torch.cat([o, park])
                 o = o.contiguous()
-                self.scatter_argmax(self.model(self.gather(scene, o)), o, mosaic)
+                for c0 in range(0, o.shape[0], self.engine_batch):
+                    oc = o[c0:c0 + self.engine_batch]
+                    self.scatter_argmax(self.model(self.gather(scene, oc)), oc, mosaic)
         finally:
             self.model.train(was_training)
-        if reduce and self.world_size > 1:
-            # per-rank mosaics are disjoint and zero elsewhere: SUM == union (uint8 is a native NCCL type)
+        return self.assemble(mosaic) if reduce else mosaic
+
+    def assemble(self, mosaic: torch.Tensor) -> torch.Tensor:
+        """Union of the per-rank mosaics on every rank: they are disjoint and zero elsewhere, so SUM == union (uint8 is
+        a native NCCL / gloo type).  The only exchange of the predict path."""
+        if self.world_size > 1:
             torch.distributed.all_reduce(mosaic, op=torch.distributed.ReduceOp.SUM)
         return mosaic
 

@@ -78,3 +78,18 @@ def drop_connect_masks(n_blocks: int, batch: int, rate: float | None, seed: int 
     u = rs.random_sample((n_blocks, batch)).astype(np.float32)
     keep = (1.0 - rate * (np.arange(n_blocks) / n_blocks)).astype(np.float32)
     return torch.from_numpy(np.floor(keep[:, None] + u)), torch.from_numpy(keep)
+
+
+# per-class, per-band spectral signatures of the "learnable" synthetic tiles (rows: classes 0..3, columns: 6 bands)
+_SIGNATURES = ((0.0, 0.0, 0.0, 0.0, 0.0, 0.0), (0.9, -0.6, 0.4, -0.8, 0.2, 0.7), (-0.7, 0.8, -0.5, 0.6, -0.9, 0.1),
+               (0.3, 0.5, 0.9, -0.2, 0.8, -0.8))
+
+
+def signal_tiles(lab: torch.Tensor, channels: int = 6, seed: int = 4321, noise: float = 0.6) -> torch.Tensor:
+    """fp32 [B, C, H, W] tiles that CARRY the label: per-class band signature + N(0, noise^2).  Real Sentinel-2 tiles
+    correlate with land cover; i.i.d. noise tiles do not, so a net trained on them can only memorise.  Used by the
+    well-conditioned ("trained") parity fixture: after a few hundred Adam steps the logits separate."""
+    rs = np.random.RandomState(seed)
+    sig = torch.tensor(_SIGNATURES, dtype=torch.float32)[:, :channels]          # [classes, C]
+    base = sig[lab].permute(0, 3, 1, 2).contiguous()                            # [B, C, H, W]
+    return base + noise * torch.from_numpy(rs.standard_normal(tuple(base.shape)).astype(np.float32))

@@ -44,15 +44,48 @@ class FusedAdam:
         self.exp_avg_sq = torch.zeros_like(self.flat_param)
         self.step_count = 0
         self.lib = L.load()
+        self._table, self._n_entries, self._table_version, self._table_dtypes, self._table_complete = None, 0, -1, [], False
+
+    def _entry_table(self):
+        """Device table of every packed tensor-core weight operand (all dtypes), sorted by flat parameter offset;
+        rebuilt when the engine has created new packed weights."""
+        eng = self.eng
+        if self._table_version != eng.packs_version:
+            base = self.flat_param.data_ptr()
+            end = base + 4 * self.flat_param.numel()
+            ents = [pw.entry(base) for d in eng.packs.values() for pw in d.values()
+                    if base <= pw.src.data_ptr() < end]
+            ents.sort(key=lambda e: e.start)
+            self._n_entries = len(ents)
+            if ents:
+                arr = (L.PackEntry * len(ents))(*ents)
+                raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+                self._table = raw.to(self.flat_param.device)
+            else:
+                self._table = None
+            self._table_dtypes = list(eng.packs.keys())
+            self._table_complete = all(base <= pw.src.data_ptr() < end for d in eng.packs.values() for pw in d.values())
+            self._table_version = eng.packs_version
+        return self._table, self._n_entries
 
     def step(self, grad_scale: float = 1.0) -> None:
+        """One launch: Adam over the flat buffer AND the re-pack of every tensor-core weight operand made from it."""
         self.step_count += 1
         st = torch.cuda.current_stream().cuda_stream
-        L.check(self.lib.s2lc_adam_step(self.flat_param.data_ptr(), self.eng.flat_grad.data_ptr(),
-                                        self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.flat_param.numel(),
-                                        self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_count,
-                                        grad_scale, st))
-        self.eng.weights_dirty = True              # packed bf16 copies must be refreshed before the next forward
+        eng = self.eng
+        if eng._ptr_signature() != eng._param_ptrs:        # parameters moved since the last forward: no packs to refresh
+            table, n = None, 0
+        else:
+            table, n = self._entry_table()
+        L.check(self.lib.s2lc_adam_pack_step(self.flat_param.data_ptr(), eng.flat_grad.data_ptr(),
+                                             self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                                             self.flat_param.numel(), self.lr, self.betas[0], self.betas[1], self.eps,
+                                             self.wd, self.step_count, grad_scale, L.ptr(table), n, st))
+        eng.weight_gen += 1                                # parameters changed behind autograd's back
+        if table is not None and self._table_complete and self._table_version == eng.packs_version:
+            sig = eng.weight_signature()                   # ... and every packed copy was refreshed in the same pass
+            for dt in self._table_dtypes:
+                eng._pack_sig[dt] = sig
 
 
 class SegmentationStep:
@@ -127,11 +160,16 @@ class DataParallelTrainer(SegmentationStep):
         if self.world > 1:   # identical initial weights on every rank (DDP broadcasts rank 0's at construction)
             dist.broadcast(self.optimizer.flat_param, src=0, group=self.pg)
 
+    snapshot: torch.Tensor | None = None   # bench.py dp_check: receives every bucket's LOCAL values at fire time
+
     def _bucket_ready(self, bucket_index: int) -> None:
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self.comm_stream.wait_event(ev)
         with torch.cuda.stream(self.comm_stream):
+            if self.snapshot is not None:
+                a, b = self.buckets[bucket_index][:2]
+                self.snapshot[a:b].copy_(self.eng.flat_grad[a:b])
             self.reducer.reduce(bucket_index)
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:

@@ -104,3 +104,16 @@ def self_noise_report(res, version: str, size: int, batch: int, loss: str = "foc
         ref32 = res["o_grads"][k].double()
         out.append((k, float((ours - g).norm()) / denom, float((ref32 - g).norm()) / denom))
     return out
+
+
+def self_noise_gate(rep, tol: float = 1e-4):
+    """The fp32 gradient gate used by the model tests and smoke(): a tensor fails if its error against the fp64
+    oracle exceeds max(tol, 4x the reference's own fp32 error on it, 4x the median reference error); the population
+    fails if its median exceeds 2x the reference's median + tol.  Returns (bad tensors, median ours, median ref)."""
+    import statistics
+    med_ref = statistics.median(e for _, _, e in rep)
+    med = statistics.median(e for _, e, _ in rep)
+    bad = [(k, eo, er) for k, eo, er in rep if eo > max(tol, 4 * er, 4 * med_ref)]
+    if med > 2 * med_ref + tol:
+        bad.append(("<median>", med, med_ref))
+    return bad, med, med_ref

@@ -19,11 +19,12 @@ BF = torch.bfloat16
 
 def _both(fn):
     """Run fn() with the streaming engine disabled (reference) and enabled; return both results."""
-    os.environ["S2LC_NO_STREAM"] = "1"
+    from s2lc_b200 import _lib
+    old = _lib.load().s2lc_set_debug_flags(1)      # bit 0: streaming engines off
     try:
         ref = fn()
     finally:
-        os.environ["S2LC_NO_STREAM"] = "0"
+        _lib.load().s2lc_set_debug_flags(old)
     got = fn()
     torch.cuda.synchronize()
     return ref, got

@@ -1,0 +1,198 @@
+"""Parity of everything bench.py times that had no test in round 1 (VERDICT r01 "next round" 1):
+
+  (a) the BENCHED configuration — b5, 512x512, bs = 32, bf16, drop-connect on, through
+      ``DataParallelTrainer.forward_backward`` — against the oracle on the same GPU under ``torch.autocast(bf16)``
+      (what Lightning's precision="bf16" runs), anchored by a three-way comparison with the fp32 oracle at bs = 8;
+  (b) ``s2lc_adam_pack_step`` (FusedAdam) against ``torch.optim.Adam(lr, weight_decay)`` incl. the re-packed operands;
+  (c) the built-in drop-connect generator ``s2lc_dropconnect_masks``;
+  plus: no bf16 conv call of a b5 step may fall back to the CUDA-core engine."""
+import math
+import statistics
+
+import pytest
+import torch
+
+from _parity import alpha_weights, build_model, rel
+from oracle import unet_oracle as O
+from s2lc_b200 import _lib, synthetic
+from s2lc_b200.losses import FocalLoss
+from s2lc_b200.train_segmentation import DataParallelTrainer, FusedAdam, SegmentationStep
+
+pytestmark = pytest.mark.gpu
+
+
+def _ours_bf16(version, size, batch, dc_rate):
+    model, sd = build_model(version, "bf16", dc_rate)
+    masks = synthetic.drop_connect_masks(len(model.encoder.specs), batch, dc_rate)
+    if masks is not None:
+        model.set_drop_connect_masks((masks[0] / masks[1][:, None]).cuda())
+    trainer = DataParallelTrainer(model, FocalLoss(alpha_weights(), 2.0, 0.0, ignore_index=0))
+    x, y = synthetic.tiles(batch, size).cuda(), synthetic.labels(batch, size).cuda()
+    _lib.load().s2lc_simt_fallbacks(1)
+    loss = trainer.forward_backward(x, y)
+    torch.cuda.synchronize()
+    fallbacks = _lib.load().s2lc_simt_fallbacks(0)
+    eng = model.engine()
+    ws = next(w for pool in eng.workspaces.values() for w in pool)
+    logits = ws.logits.view(batch, size, size, -1).permute(0, 3, 1, 2).float().cpu()
+    grads = {k: eng.grad_views[k].detach().float().cpu().clone() for k, _ in eng.used}
+    del trainer, model
+    torch.cuda.empty_cache()
+    return sd, masks, logits, float(loss), grads, fallbacks
+
+
+def _oracle(sd, masks, version, size, batch, autocast, dtype=torch.float32):
+    x, y = synthetic.tiles(batch, size).cuda(), synthetic.labels(batch, size).cuda()
+    sd_c = {k: v.cuda() for k, v in sd.items()}
+    dc = None if masks is None else (masks[0].cuda(), masks[1].cuda())
+    lg, loss, grads = O.loss_and_grads(sd_c, x, y, version, alpha=alpha_weights().cuda(), gamma=2.0, ignore_index=0,
+                                       dc_masks=dc, autocast_bf16=autocast)
+    out = lg.float().cpu(), float(loss), {k: v.float().cpu() for k, v in grads.items()}
+    del sd_c, lg, grads
+    torch.cuda.empty_cache()
+    return out
+
+
+def _grad_errs(a, b):
+    mx = max(float(v.norm()) for v in b.values())
+    return {k: float((a[k].double() - b[k].double()).norm()) / max(float(b[k].double().norm()), 1e-3 * mx) for k in b}
+
+
+def test_benched_shape_b5_512_bs32_bf16():
+    version, size, dc = "b5", 512, 0.2
+    # ---- anchor at bs = 8: ours(bf16) and reference-autocast(bf16) against the fp32 oracle (TF32 off)
+    sd, m8, l8, loss8, g8, fb8 = _ours_bf16(version, size, 8, dc)
+    r_l8, r_loss8, r_g8 = _oracle(sd, m8, version, size, 8, autocast=True)
+    f_l8, f_loss8, f_g8 = _oracle(sd, m8, version, size, 8, autocast=False)
+    e_ours, e_ref, d8 = rel(l8, f_l8), rel(r_l8, f_l8), rel(l8, r_l8)
+    agree = float((l8.argmax(1) == f_l8.argmax(1)).float().mean())
+    agree_ref = float((r_l8.argmax(1) == f_l8.argmax(1)).float().mean())
+    med_o = statistics.median(_grad_errs(g8, f_g8).values())
+    med_r = statistics.median(_grad_errs(r_g8, f_g8).values())
+    gd8 = statistics.median(_grad_errs(g8, r_g8).values())
+    print(f"\n[b5 512 bs8 bf16, drop-connect 0.2] logits rel-err vs fp32 oracle: ours {e_ours:.3e}, reference-autocast "
+          f"{e_ref:.3e}; ours vs reference-autocast {d8:.3e}; argmax agreement ours {agree:.5f}, reference-autocast "
+          f"{agree_ref:.5f}; loss ours {loss8:.6f} autocast {r_loss8:.6f} fp32 {f_loss8:.6f}; grad rel-err median ours "
+          f"{med_o:.3e} reference-autocast {med_r:.3e}; SIMT fallbacks {fb8}")
+    assert fb8 == 0
+    assert e_ours <= max(2e-2, 1.1 * e_ref)
+    assert agree >= min(0.999, agree_ref - 0.002)
+    assert abs(loss8 - f_loss8) <= max(2e-2, 2 * abs(r_loss8 - f_loss8) / abs(f_loss8)) * abs(f_loss8)
+    assert med_o <= max(2e-2, 1.5 * med_r)
+    # ---- the benched shape: bs = 32 (bs = 16 if the eager autocast oracle does not fit beside the engine)
+    batch = 32
+    sd, m, l, loss, g, fb = _ours_bf16(version, size, batch, dc)
+    try:
+        r_l, r_loss, r_g = _oracle(sd, m, version, size, batch, autocast=True)
+    except torch.OutOfMemoryError:
+        torch.cuda.empty_cache()
+        batch = 16
+        sd, m, l, loss, g, fb = _ours_bf16(version, size, batch, dc)
+        r_l, r_loss, r_g = _oracle(sd, m, version, size, batch, autocast=True)
+    d = rel(l, r_l)
+    agree_b = float((l.argmax(1) == r_l.argmax(1)).float().mean())
+    agree_b8 = float((l8.argmax(1) == r_l8.argmax(1)).float().mean())
+    ge = _grad_errs(g, r_g)
+    gd = statistics.median(ge.values())
+    worst = max(ge.items(), key=lambda kv: kv[1])
+    print(f"[b5 512 bs{batch} bf16, drop-connect 0.2 — the benched shape] ours vs reference-autocast: logits rel-err {d:.3e} "
+          f"(bs8: {d8:.3e}), argmax agreement {agree_b:.5f} (bs8: {agree_b8:.5f}), loss {loss:.6f} vs {r_loss:.6f}, grad "
+          f"rel-err median {gd:.3e} (bs8: {gd8:.3e}), worst {worst[1]:.3e} ({worst[0]}); SIMT fallbacks {fb}")
+    assert fb == 0
+    assert all(math.isfinite(float(v.abs().max())) for v in g.values())
+    # two bf16 evaluations of the same net: their distance is bounded by the sum of their distances to fp32
+    assert d <= 1.25 * max(d8, e_ours + e_ref)
+    assert agree_b >= agree_b8 - 0.01
+    assert abs(loss - r_loss) <= 2e-2 * abs(r_loss)
+    assert gd <= 1.5 * max(gd8, med_o + med_r)
+
+
+def test_adam_kernel_matches_torch():
+    """s2lc_adam_pack_step vs torch.optim.Adam(lr, weight_decay=L2) for 10 steps on one flat buffer (<= 1e-6)."""
+    lib = _lib.load()
+    g = torch.Generator(device="cuda").manual_seed(7)
+    n = 1_000_003
+    p0 = torch.randn(n, generator=g, device="cuda") * 0.1
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([ref], lr=1e-3, weight_decay=0.05)
+    p, m, v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+    st = torch.cuda.current_stream().cuda_stream
+    for step in range(1, 11):
+        grad = torch.randn(n, generator=g, device="cuda") * (0.01 if step % 2 else 1.0)
+        ref.grad = grad.clone()
+        opt.step()
+        _lib.check(lib.s2lc_adam_pack_step(p.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), n, 1e-3, 0.9,
+                                           0.999, 1e-8, 0.05, step, 1.0, None, 0, st))
+        assert rel(p, ref.detach()) <= 1e-6, step
+    assert rel(m, opt.state[ref]["exp_avg"]) <= 1e-6
+    assert rel(v, opt.state[ref]["exp_avg_sq"]) <= 1e-6
+
+
+def test_fused_step_matches_torch_adam_and_repacks():
+    """SegmentationStep(fused) vs the same engine's gradients fed to torch.optim.Adam, 3 steps, identical injected
+    drop-connect masks; afterwards every packed bf16 operand must equal a fresh pack of the stepped parameters."""
+    torch.manual_seed(0)
+    ma, sd = build_model("b0", "bf16", 0.2)
+    mb, _ = build_model("b0", "bf16", 0.2)
+    masks = synthetic.drop_connect_masks(len(ma.encoder.specs), 4, 0.2)
+    dc = (masks[0] / masks[1][:, None]).cuda()
+    ma.set_drop_connect_masks(dc)
+    mb.set_drop_connect_masks(dc)
+    fn = FocalLoss(alpha_weights(), 2.0, 0.0, ignore_index=0)
+    sa = SegmentationStep(ma, fn, lr=1e-3, weight_decay=0.05, fused_optimizer=True)
+    sb = SegmentationStep(mb, fn, lr=1e-3, weight_decay=0.05, fused_optimizer=False)
+    x, y = synthetic.tiles(4, 128).cuda(), synthetic.labels(4, 128).cuda()
+    for _ in range(3):
+        la, lb = sa(x, y), sb(x, y)
+    torch.cuda.synchronize()
+    pa, pb = dict(ma.named_parameters()), dict(mb.named_parameters())
+    worst = max((rel(pa[k], pb[k]), k) for k in pa)
+    # the two runs see independently rounded bf16 gradients (fp32 atomics order), and Adam's first steps are
+    # sign-like: a parameter whose gradient is at the noise floor may move by lr in either direction
+    med = statistics.median(rel(pa[k], pb[k]) for k in pa)
+    print(f"\nfused Adam vs torch Adam after 3 steps: median param rel diff {med:.2e}, worst {worst[0]:.2e} ({worst[1]})")
+    assert med <= 1e-5
+    assert abs(float(la) - float(lb)) <= 2e-2 * abs(float(lb))
+    # re-pack: what the fused pass scattered == a from-scratch pack of the current parameters
+    eng = ma.engine()
+    lib = _lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    assert eng._pack_sig.get(torch.bfloat16) == eng.weight_signature()     # the fused pass marked them clean
+    n_checked = 0
+    for key, pw in eng.packs[torch.bfloat16].items():
+        have = pw.buf.clone()
+        _lib.check(lib.s2lc_weight_pack(*pw.args, st))
+        assert torch.equal(have, pw.buf), key
+        n_checked += 1
+    assert n_checked > 50
+
+
+def test_dropconnect_generator():
+    """Values in {0, 1/keep_i}; block 0 never drops; the keep rate of block i is 1 - rate*i/n (reference
+    efficientnet_unet.py:257, :390-398) inside a 4.5-sigma binomial interval; draws differ between steps and are
+    reproducible for one (seed, step)."""
+    lib = _lib.load()
+    nb, batch, rate = 39, 8192, 0.2
+    st = torch.cuda.current_stream().cuda_stream
+
+    def draw(step):
+        out = torch.empty(nb, batch, device="cuda")
+        _lib.check(lib.s2lc_dropconnect_masks(out.data_ptr(), nb, batch, rate, 0x5eed, step, st))
+        return out
+
+    a, b, a2 = draw(1), draw(2), draw(1)
+    assert torch.equal(a, a2)
+    assert not torch.equal(a, b)
+    assert torch.all(a[0] == 1.0)
+    for i in range(nb):
+        keep = 1.0 - rate * i / nb
+        row = a[i]
+        kept = row != 0
+        assert torch.allclose(row[kept], torch.full_like(row[kept], 1.0 / keep), rtol=1e-6)
+        frac = float(kept.float().mean())
+        sigma = math.sqrt(keep * (1 - keep) / batch)
+        assert abs(frac - keep) <= 4.5 * sigma + 1e-9, (i, frac, keep)
+    # independence between blocks / steps: the two draws agree about as often as independent coins would
+    same = float(((a[20] != 0) == (b[20] != 0)).float().mean())
+    k = 1.0 - rate * 20 / nb
+    assert abs(same - (k * k + (1 - k) * (1 - k))) < 0.03

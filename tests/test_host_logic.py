@@ -225,36 +225,52 @@ def test_rank_batches_partition_the_tiles(n_tiles, batch, world):
 def _mosaic_worker(rank: int, world: int, port: int, ret) -> None:
     import numpy as np
     from oracle.mosaic_oracle import write_tile
-    from s2lc_b200.inference import plan_mosaic, rank_batches
+    from s2lc_b200.inference import MosaicPredictor, plan_mosaic
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         h, w, tile, margin, batch = 150, 200, 96, 16, 4
         origins = plan_mosaic(h, w, tile, margin)
+        index_of = {tuple(o): i for i, o in enumerate(origins.tolist())}
 
         def tile_logits(i):                     # class (i % 5) + 1 everywhere: which tile wrote a pixel stays visible
             lg = np.zeros((7, tile, tile), dtype=np.float32)
             lg[i % 5 + 1] = 1.0
             return lg
 
+        class HostStages(MosaicPredictor):
+            """MosaicPredictor with its two CUDA stages replaced by the numpy oracle, so that predict() itself — tile
+            planning, dealing batches to ranks, parking the ragged last batch, engine chunks, the final all-reduce —
+            runs on the CPU over gloo."""
+            calls = 0
+
+            def gather(self, scene, o):
+                return o                         # the "network" below is the identity: hand the origins through
+
+            def scatter_argmax(self, logits, o, mosaic):
+                HostStages.calls += 1
+                assert o.shape[0] <= self.engine_batch
+                buf = mosaic.numpy()
+                for t, l in o.tolist():
+                    if (t, l) in index_of:       # parked tiles lie outside the scene and write nothing
+                        write_tile(buf, tile_logits(index_of[(t, l)]), t, l, margin)
+
         full = np.zeros((h, w), dtype=np.uint8)
         for i, (t, l) in enumerate(origins.tolist()):
             write_tile(full, tile_logits(i), t, l, margin)
-        mine = np.zeros((h, w), dtype=np.uint8)
-        for s, e in rank_batches(origins.shape[0], batch, rank, world):
-            for i in range(s, e):
-                t, l = origins[i].tolist()
-                write_tile(mine, tile_logits(i), t, l, margin)
-        mosaic = torch.from_numpy(mine)
-        dist.all_reduce(mosaic, op=dist.ReduceOp.SUM)     # what MosaicPredictor.predict does with the per-rank buffers
-        ret[rank] = bool(np.array_equal(mosaic.numpy(), full)) and bool((full > 0).all())
+        pred = HostStages(torch.nn.Identity(), np.zeros(6, np.float32), np.ones(6, np.float32), tile=tile, margin=margin,
+                          batch=batch, device="cpu", engine_batch=2)
+        assert (pred.rank, pred.world_size) == (rank, world)
+        mosaic = pred.predict(torch.zeros(6, h, w, dtype=torch.int16))
+        ret[rank] = (bool(np.array_equal(mosaic.numpy(), full)) and bool((full > 0).all()) and HostStages.calls >= 2)
     finally:
         dist.destroy_process_group()
 
 
 def test_two_rank_mosaic_assembly_gloo():
-    """Mosaic inference at world_size 2 over gloo: batches of tiles dealt round-robin to the ranks
-    fill disjoint parts of zero-initialised uint8 buffers, so one SUM all-reduce assembles the scene on every rank."""
+    """Mosaic inference at world_size 2 over gloo THROUGH MosaicPredictor.predict (its CUDA stages
+    swapped for the numpy oracle): batches of tiles dealt round-robin to the ranks fill disjoint parts of
+    zero-initialised uint8 buffers, and one SUM all-reduce assembles the scene on every rank."""
     world, port = 2, _free_port()
     with mp.Manager() as mgr:
         ret = mgr.dict()

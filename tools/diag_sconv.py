@@ -21,8 +21,8 @@ for (cin, cout, n, h, w, only_tap) in [(32, 32, 1, 8, 128, None), (32, 32, 1, 8,
     pw = pack(lib, wt, BF, 1, 1, cout, 9, cin, 0, cin * 9, 1, 9, cpad=(cin + 63) // 64 * 64)
     lz = lazy(xr, cin)
     res = {}
-    for name, env in [("tile", {"S2LC_NO_STREAM": "1"}), ("stream", {"S2LC_NO_STREAM": "0"})]:
-        os.environ.update(env)
+    for name, flag in [("tile", 1), ("stream", 0)]:
+        lib.s2lc_set_debug_flags(flag)
         out = torch.zeros(rows, cout, dtype=BF, device="cuda")
         run_conv(lib, 1, 1, lz, n, h, w, cin, pw, out, cout)
         torch.cuda.synchronize()
