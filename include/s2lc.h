@@ -250,9 +250,10 @@ int32_t s2lc_argmax_mosaic(const void* logits, int64_t ld, const int32_t* origin
                            int64_t ld_mosaic, int32_t B, int32_t tile, int32_t margin, int32_t Hm, int32_t Wm,
                            int32_t n_classes, int32_t dtype, void* stream);
 
-/* ---- optimizer (next row f1): torch.optim.Adam with L2 weight decay, train_segmentation.py:110-114 */
-int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
-                       float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+/* ---- optimizer (next row f1): torch.optim.Adam with L2 weight decay, train_segmentation.py:110-114.
+ * Hyper-parameters are doubles, as torch holds them: 1 - beta2 formed in fp32 from 0.999f is off by 1.3e-5. */
+int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr,
+                       double beta1, double beta2, double eps, double weight_decay, int64_t step, float grad_scale,
                        void* stream);
 
 /* Adam + re-pack of the tensor-core weight operands in ONE pass over the flat parameter buffer (row f1 as SURVEY.md
@@ -268,8 +269,8 @@ typedef struct {
   int32_t role[4];
   int32_t N2, Tt, Cpad, Kpad, flip, dtype;
 } s2lc_pack_entry;
-int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
-                            float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr,
+                            double beta1, double beta2, double eps, double weight_decay, int64_t step, float grad_scale,
                             const s2lc_pack_entry* entries, int32_t n_entries, void* stream);
 
 /* ---- diagnostics.  s2lc_simt_fallbacks: number of bf16 conv / weight-gradient calls since load that no tcgen05 engine

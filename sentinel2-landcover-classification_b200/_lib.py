@@ -91,8 +91,8 @@ _PROTOS = {
     "s2lc_dropconnect_masks": ([vp, i32, i32, f32, u64, u64, vp], i32),
     "s2lc_loss_fwd_bwd": ([vp, i64, vp, vp, f32, f32, i64, i32, i32, vp, vp, vp, i64, i64, i32, i32, vp], i32),
     "s2lc_scale_inplace": ([vp, i64, vp, i64, i32, i32, vp], i32),
-    "s2lc_adam_step": ([vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, vp], i32),
-    "s2lc_adam_pack_step": ([vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i64, f32, vp, i32, vp], i32),
+    "s2lc_adam_step": ([vp, vp, vp, vp, i64, f64, f64, f64, f64, f64, i64, f32, vp], i32),
+    "s2lc_adam_pack_step": ([vp, vp, vp, vp, i64, f64, f64, f64, f64, f64, i64, f32, vp, i32, vp], i32),
     "s2lc_simt_fallbacks": ([i32], i64),
     "s2lc_num_sms": ([], i32),
     "s2lc_set_debug_flags": ([C.c_uint32], C.c_uint32),

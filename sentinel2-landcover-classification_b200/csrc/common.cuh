@@ -75,7 +75,9 @@ template <> struct Vec8<float> {
 };
 
 // ------------------------------------------------------------------ activations
-__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+// exact form (expf, IEEE division): the fp32 verification engines and the tiny squeeze-excite FCs; the bf16-storage
+// streaming kernels use the one-MUFU forms below through act_fwd_t / act_bwd_t
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
 __device__ __forceinline__ float act_fwd(float u, int act) {
   if (act == S2LC_ACT_SILU) return u * sigmoidf_(u);
   if (act == S2LC_ACT_RELU) return fmaxf(u, 0.f);
@@ -113,6 +115,14 @@ __device__ __forceinline__ float act_bwd_fast(float u, int act) {
   }
   if (act == S2LC_ACT_RELU) return u > 0.f ? 1.f : 0.f;
   return 1.f;
+}
+
+// by storage type: bf16 -> one-MUFU forms, fp32 -> exact forms
+template <typename T> __device__ __forceinline__ float act_fwd_t(float u, int act) {
+  return sizeof(T) == 2 ? act_fwd_fast(u, act) : act_fwd(u, act);
+}
+template <typename T> __device__ __forceinline__ float act_bwd_t(float u, int act) {
+  return sizeof(T) == 2 ? act_bwd_fast(u, act) : act_bwd(u, act);
 }
 
 // ------------------------------------------------------------------ lazy sources, element-wise (generic path)

@@ -72,7 +72,7 @@ struct LazyFetch {
     }
     if (L.act != S2LC_ACT_NONE) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j], L.act);
+      for (int j = 0; j < 8; ++j) v[j] = act_fwd_t<T>(v[j], L.act);
     }
   }
 };
@@ -203,8 +203,8 @@ __global__ void __launch_bounds__(256) dwconv_kernel(s2lc_lazy in, s2lc_lazygrad
           if (has_prev) {
             float2 z = ld2<T>(reinterpret_cast<const T*>(prev.raw) + orow * prev.ld + c);
             za = z.x; zb = z.y;
-            a *= act_bwd(za * psc0 + psh0, prev.act);
-            b *= act_bwd(zb * psc1 + psh1, prev.act);
+            a *= act_bwd_t<T>(za * psc0 + psh0, prev.act);
+            b *= act_bwd_t<T>(zb * psc1 + psh1, prev.act);
           }
           if (res) {
             float2 e = ld2<T>(res + orow * ld_res + c);
@@ -301,8 +301,8 @@ __global__ void __launch_bounds__(256) dwconv_bwd_data_s2_kernel(s2lc_lazygrad g
         if (has_prev) {
           float2 z = ld2<T>(reinterpret_cast<const T*>(prev.raw) + orow * prev.ld + c);
           za = z.x; zb = z.y;
-          a *= act_bwd(za * psc0 + psh0, prev.act);
-          b *= act_bwd(zb * psc1 + psh1, prev.act);
+          a *= act_bwd_t<T>(za * psc0 + psh0, prev.act);
+          b *= act_bwd_t<T>(zb * psc1 + psh1, prev.act);
         }
         if (res) {
           float2 e = ld2<T>(res + orow * ld_res + c);

@@ -186,7 +186,7 @@ __global__ void bn_apply_kernel(s2lc_lazy in, const T* __restrict__ res, int64_t
       Vec8<T>::load(raw + r * in.ld + cv * 8, v);
       float rs = rowscale ? rowscale[r / HW] : 1.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j] * sc[j] + sh[j], in.act) * rs;
+      for (int j = 0; j < 8; ++j) v[j] = act_fwd_t<T>(v[j] * sc[j] + sh[j], in.act) * rs;
       if (res) {
         float e[8];
         Vec8<T>::load(res + r * ld_res + cv * 8, e);
@@ -259,68 +259,73 @@ constexpr int SE_APPLY_BLOCKS_PER_SM = 3;   // se_bwd_apply holds 4 per-channel 
 // pooled[n, c] = (1/HW) * sum_{rows of sample n} act(z*scale+shift), split over gridDim.x blocks per sample
 template <typename T, bool WITH_DA>
 __global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t ld_da, float* __restrict__ out, int HW,
-                               int C, float mul, float* __restrict__ part, unsigned* __restrict__ counter) {
-  // grid: (splits, N).  WITH_DA: out[n,c] += sum da*act(u)  (d gate), else mean of act(u).
+                               int C, float mul, float* __restrict__ part, unsigned* __restrict__ counter, int VS) {
+  // grid: (blocks per sample, N).  WITH_DA: out[n,c] = sum da*act(u)  (d gate), else mean of act(u).
+  // The rows of a sample are dealt to VS VIRTUAL splits, VS a function of (HW, C) only; a block walks the virtual
+  // splits blockIdx.x, blockIdx.x + gridDim.x, ...  Every partial therefore sums the same rows in the same order
+  // whatever the batch size or the grid: the result is bit-identical run to run AND across batch sizes.
   const int CV = C / 8;
   ChanIter it(CV);
   const int n = blockIdx.y;
   const T* raw = reinterpret_cast<const T*>(in.raw) + (int64_t)n * HW * in.ld;
   const T* dap = WITH_DA ? da + (int64_t)n * HW * ld_da : nullptr;
   extern __shared__ float smem[];
-  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
-    int cv = cv0 + it.c_local;
-    float acc[8] = {};
-    if (it.active && cv < CV) {
-      float sc[8], sh[8];
+  for (int vs = blockIdx.x; vs < VS; vs += gridDim.x) {
+    for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+      int cv = cv0 + it.c_local;
+      float acc[8] = {};
+      if (it.active && cv < CV) {
+        float sc[8], sh[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        sc[j] = in.scale ? in.scale[cv * 8 + j] : 1.f;
-        sh[j] = in.shift ? in.shift[cv * 8 + j] : 0.f;
-      }
-      constexpr int U = SeU<T>::value;
-      const int stride = gridDim.x * it.rows_par;
-      for (int r = blockIdx.x * it.rows_par + it.r_local; r < HW; r += U * stride) {
-        RawV8<T> rv[U], rd[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int rr = r + u * stride;
-          if (rr < HW) {
-            rv[u].load(raw + (int64_t)rr * in.ld + cv * 8);
-            if (WITH_DA) rd[u].load(dap + (int64_t)rr * ld_da + cv * 8);
-          }
+        for (int j = 0; j < 8; ++j) {
+          sc[j] = in.scale ? in.scale[cv * 8 + j] : 1.f;
+          sh[j] = in.shift ? in.shift[cv * 8 + j] : 0.f;
         }
+        constexpr int U = SeU<T>::value;
+        const int stride = VS * it.rows_par;
+        for (int r = vs * it.rows_par + it.r_local; r < HW; r += U * stride) {
+          RawV8<T> rv[U], rd[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          if (r + u * stride < HW) {
-            float v[8], d[8];
-            rv[u].unpack(v);
-            if (WITH_DA) rd[u].unpack(d);
+          for (int u = 0; u < U; ++u) {
+            const int rr = r + u * stride;
+            if (rr < HW) {
+              rv[u].load(raw + (int64_t)rr * in.ld + cv * 8);
+              if (WITH_DA) rd[u].load(dap + (int64_t)rr * ld_da + cv * 8);
+            }
+          }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float a = act_fwd(fmaf(v[j], sc[j], sh[j]), in.act);
-              acc[j] = WITH_DA ? fmaf(d[j], a, acc[j]) : acc[j] + a;
+          for (int u = 0; u < U; ++u) {
+            if (r + u * stride < HW) {
+              float v[8], d[8];
+              rv[u].unpack(v);
+              if (WITH_DA) rd[u].unpack(d);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float a = act_fwd_t<T>(fmaf(v[j], sc[j], sh[j]), in.act);
+                acc[j] = WITH_DA ? fmaf(d[j], a, acc[j]) : acc[j] + a;
+              }
             }
           }
         }
       }
-    }
-    // DETERMINISTIC reduction (two identical predictions must give identical class maps): the rows_par threads that
-    // share a channel vector are summed in index order through shared memory, ...
-    const int nsm = it.cvb * 8;
-    if (it.active) {
+      // DETERMINISTIC reduction: the rows_par threads that share a channel vector are summed in index order through
+      // shared memory, ...
+      const int nsm = it.cvb * 8;
+      if (it.active) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) smem[(it.r_local * it.cvb + it.c_local) * 8 + j] = (cv < CV) ? acc[j] : 0.f;
+        for (int j = 0; j < 8; ++j) smem[(it.r_local * it.cvb + it.c_local) * 8 + j] = (cv < CV) ? acc[j] : 0.f;
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < nsm; i += blockDim.x) {
+        float t = 0.f;
+        for (int r = 0; r < it.rows_par; ++r) t += smem[r * nsm + i];
+        int c = cv0 * 8 + i;
+        if (c < C) part[((int64_t)n * VS + vs) * C + c] = t;
+      }
+      __syncthreads();
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < nsm; i += blockDim.x) {
-      float t = 0.f;
-      for (int r = 0; r < it.rows_par; ++r) t += smem[r * nsm + i];
-      int c = cv0 * 8 + i;
-      if (c < C) part[((int64_t)n * gridDim.x + blockIdx.x) * C + c] = t;
-    }
-    __syncthreads();
   }
-  // ... and the per-block partials of a sample by the LAST block to finish, again in index order.
+  // ... and the VS partials of a sample by the LAST block to finish, again in index order.
   __shared__ unsigned ticket;
   __threadfence();
   __syncthreads();
@@ -330,7 +335,7 @@ __global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_laz
     __threadfence();
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       float t = 0.f;
-      for (int sidx = 0; sidx < (int)gridDim.x; ++sidx) t += __ldcg(&part[((int64_t)n * gridDim.x + sidx) * C + c]);
+      for (int sidx = 0; sidx < VS; ++sidx) t += __ldcg(&part[((int64_t)n * VS + sidx) * C + c]);
       out[(int64_t)n * C + c] = t * mul;
     }
     if (threadIdx.x == 0) counter[n] = 0u;    // ready for the next launch on this stream
@@ -512,7 +517,7 @@ __global__ void __launch_bounds__(256, SE_APPLY_BLOCKS_PER_SM) se_bwd_apply_kern
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               float pre = z[j] * sc[j] + sh[j];
-              float v = roundf_as<T>((d[j] * g[j] + dp[j]) * act_bwd(pre, in.act));
+              float v = roundf_as<T>((d[j] * g[j] + dp[j]) * act_bwd_t<T>(pre, in.act));
               d[j] = v;
               acc[0][j] += v;
               acc[1][j] += v * z[j];
@@ -692,17 +697,17 @@ __global__ void scale_inplace_kernel(T* x, int64_t ld, const float* factor, int6
 
 // ------------------------------------------------------------------------------------------ Adam (L2 decay)
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                            float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps, float wd,
-                            float bc1, float bc2_sqrt, float gscale) {
+                            float* __restrict__ v, int64_t n, float step_size, float b1, float b2, float omb1, float omb2, float eps,
+                            float wd, float bc2_sqrt, float gscale) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float pi = p[i];
     float gi = g[i] * gscale + wd * pi;
-    float mi = b1 * m[i] + (1.f - b1) * gi;
-    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    float mi = b1 * m[i] + omb1 * gi;
+    float vi = b2 * v[i] + omb2 * gi * gi;
     m[i] = mi;
     v[i] = vi;
     float denom = sqrtf(vi) / bc2_sqrt + eps;
-    p[i] = pi - (lr / bc1) * (mi / denom);
+    p[i] = pi - step_size * (mi / denom);
   }
 }
 
@@ -721,6 +726,9 @@ __device__ __forceinline__ void pack_scatter(const s2lc_pack_entry& e, int64_t r
       r -= q * s;
     }
   }
+  // a pack may take a SLICE of the source along n2 (the data-gradient operand of the first decoder conv keeps the
+  // 32 up-sampled input channels of a 38-channel weight): elements outside the slice have no packed copy
+  if (idx[1] >= e.N2 || idx[3] >= e.Cpad) return;
   const int n = idx[0] * e.N2 + idx[1];
   const int tap = e.flip ? (e.Tt - 1 - idx[2]) : idx[2];
   const int64_t di = (int64_t)n * e.Kpad + (int64_t)tap * e.Cpad + idx[3];
@@ -730,18 +738,18 @@ __device__ __forceinline__ void pack_scatter(const s2lc_pack_entry& e, int64_t r
 
 __global__ void __launch_bounds__(256) adam_pack_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                         float* __restrict__ m, float* __restrict__ v, int64_t n,
-                                                        float lr, float b1, float b2, float eps, float wd, float bc1,
-                                                        float bc2_sqrt, float gscale,
+                                                        float step_size, float b1, float b2, float omb1, float omb2,
+                                                        float eps, float wd, float bc2_sqrt, float gscale,
                                                         const s2lc_pack_entry* __restrict__ ent, int n_ent) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float pi = p[i];
     float gi = g[i] * gscale + wd * pi;
-    float mi = b1 * m[i] + (1.f - b1) * gi;
-    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    float mi = b1 * m[i] + omb1 * gi;
+    float vi = b2 * v[i] + omb2 * gi * gi;
     m[i] = mi;
     v[i] = vi;
     float denom = sqrtf(vi) / bc2_sqrt + eps;
-    pi = pi - (lr / bc1) * (mi / denom);
+    pi = pi - step_size * (mi / denom);
     p[i] = pi;
     // last entry with start <= i
     int lo = 0, hi = n_ent;
@@ -942,6 +950,23 @@ static inline int se_splits(int N, int HW, int C, int blocks_per_sm = SE_BLOCKS_
   return s < 1 ? 1 : s;
 }
 
+// Virtual splits of the deterministic pooling: a power of two that depends on (HW, C) ONLY (<= 32, >= 4 row groups of
+// work each), and the grid along x = the largest power of two <= min(VS, resident blocks / N).
+static inline int se_vsplits(int HW, int C) {
+  int cvb = C / 8 < 256 ? C / 8 : 256;
+  int rows_par = 256 / cvb;
+  int maxs = (HW + rows_par * 4 - 1) / (rows_par * 4);
+  int vs = 1;
+  while (vs * 2 <= maxs && vs < 32) vs *= 2;
+  return vs;
+}
+static inline int se_pool_blocks(int N, int VS) {
+  int want = (kNumSMs * SE_BLOCKS_PER_SM) / N;
+  int b = 1;
+  while (b * 2 <= want && b * 2 <= VS) b *= 2;
+  return b;
+}
+
 // Library-owned scratch of the deterministic squeeze-excite reductions: per-block partials [N][splits][C] and one
 // arrival counter per sample (zero between launches).  Cached per device, grown on demand (include/s2lc.h: "the
 // library never allocates persistent device memory except a cached, size-keyed workspace pool").  One stream per
@@ -971,24 +996,26 @@ static int32_t se_scratch(int N, size_t floats, float** part, unsigned** counter
 int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, int32_t C, int32_t dtype,
                      void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0, S2LC_ERR_ALIGN, "se_pool: alignment (C=%d)", C);
-  dim3 grid(se_splits(N, HW, C), N);
+  const int VS = se_vsplits(HW, C);
+  dim3 grid(se_pool_blocks(N, VS), N);
   float* part; unsigned* counter;
-  int32_t rc = se_scratch(N, (size_t)N * grid.x * C, &part, &counter);
+  int32_t rc = se_scratch(N, (size_t)N * VS * C, &part, &counter);
   if (rc) return rc;
   DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, 256, 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
-                        *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW, part, counter)));
+                        *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW, part, counter, VS)));
   return check_launch("se_pool");
 }
 
 int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, float* dgate, int32_t N, int32_t HW,
                            int32_t C, int32_t dtype, void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_da % 8 == 0, S2LC_ERR_ALIGN, "se_bwd_reduce: alignment (C=%d)", C);
-  dim3 grid(se_splits(N, HW, C), N);
+  const int VS = se_vsplits(HW, C);
+  dim3 grid(se_pool_blocks(N, VS), N);
   float* part; unsigned* counter;
-  int32_t rc = se_scratch(N, (size_t)N * grid.x * C, &part, &counter);
+  int32_t rc = se_scratch(N, (size_t)N * VS * C, &part, &counter);
   if (rc) return rc;
   DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, 256, 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
-                        *in, (const T*)da, ld_da, dgate, HW, C, 1.f, part, counter)));
+                        *in, (const T*)da, ld_da, dgate, HW, C, 1.f, part, counter, VS)));
   return check_launch("se_bwd_reduce");
 }
 
@@ -1100,14 +1127,14 @@ int32_t s2lc_scale_inplace(void* x, int64_t ld, const float* factor_dev, int64_t
   return check_launch("scale_inplace");
 }
 
-int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
-                       float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr,
+                       double beta1, double beta2, double eps, double weight_decay, int64_t step, float grad_scale,
                        void* stream) {
-  double bc1 = 1.0 - pow((double)beta1, (double)step);
-  double bc2 = 1.0 - pow((double)beta2, (double)step);
-  adam_kernel<<<grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
-                                                                      beta2, eps, weight_decay, (float)bc1,
-                                                                      (float)sqrt(bc2), grad_scale);
+  double bc1 = 1.0 - pow(beta1, (double)step);
+  double bc2 = 1.0 - pow(beta2, (double)step);
+  adam_kernel<<<grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(
+      param, grad, exp_avg, exp_avg_sq, n, (float)(lr / bc1), (float)beta1, (float)beta2, (float)(1.0 - beta1),
+      (float)(1.0 - beta2), (float)eps, (float)weight_decay, (float)sqrt(bc2), grad_scale);
   return check_launch("adam_step");
 }
 
@@ -1123,16 +1150,15 @@ uint32_t s2lc_set_debug_flags(uint32_t flags) {
   return old;
 }
 
-int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
-                            float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr,
+                            double beta1, double beta2, double eps, double weight_decay, int64_t step, float grad_scale,
                             const s2lc_pack_entry* entries, int32_t n_entries, void* stream) {
   S2LC_REQUIRE(n_entries == 0 || entries != nullptr, S2LC_ERR_SHAPE, "adam_pack_step: null entry table");
-  double bc1 = 1.0 - pow((double)beta1, (double)step);
-  double bc2 = 1.0 - pow((double)beta2, (double)step);
-  adam_pack_kernel<<<grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr,
-                                                                           beta1, beta2, eps, weight_decay, (float)bc1,
-                                                                           (float)sqrt(bc2), grad_scale, entries,
-                                                                           n_entries);
+  double bc1 = 1.0 - pow(beta1, (double)step);
+  double bc2 = 1.0 - pow(beta2, (double)step);
+  adam_pack_kernel<<<grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(
+      param, grad, exp_avg, exp_avg_sq, n, (float)(lr / bc1), (float)beta1, (float)beta2, (float)(1.0 - beta1),
+      (float)(1.0 - beta2), (float)eps, (float)weight_decay, (float)sqrt(bc2), grad_scale, entries, n_entries);
   return check_launch("adam_pack_step");
 }
 

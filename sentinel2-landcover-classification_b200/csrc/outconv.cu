@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(OC_THREADS) outconv_fwd_kernel(s2lc_lazy in, c
     for (int k = 0; k < NCLS; ++k) acc[k] = 0.f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float a = act_fwd(fmaf(v[j], sc[j], sh[j]), in.act);
+      float a = act_fwd_t<T>(fmaf(v[j], sc[j], sh[j]), in.act);
       if (sizeof(T) == 2) a = roundf_as<T>(a);   // the tensor-core engine rounds its A operand to bf16: same values
 #pragma unroll
       for (int k = 0; k < NCLS; ++k) acc[k] = fmaf(a, wr[k][j], acc[k]);
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(OC_THREADS) outconv_bwd_kernel(s2lc_lazy in, c
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float u = fmaf(z[j], sc[j], sh[j]);
-      float a = act_fwd(u, in.act);
+      float a = act_fwd_t<T>(u, in.act);
       if (sizeof(T) == 2) a = roundf_as<T>(a);
       float d = 0.f;
 #pragma unroll
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(OC_THREADS) outconv_bwd_kernel(s2lc_lazy in, c
         gw[k][j] = fmaf(g[k], a, gw[k][j]);
         d = fmaf(g[k], wr[k][j], d);
       }
-      d = roundf_as<T>(d * act_bwd(u, in.act));
+      d = roundf_as<T>(d * act_bwd_t<T>(u, in.act));
       o[j] = d;
       s0[j] += d;
       s1[j] = fmaf(d, z[j], s1[j]);

@@ -48,6 +48,16 @@ def operand(x_rows, n, h, w, sc=None, sh=None, act=0, gate=None):
     return bfr(a)
 
 
+def db_err(db, dy_rows, z_rows, n, h, w, p, q, t):
+    """The bias gradient is the per-channel sum of the gradient; an engine may sum it before or after the bf16
+    rounding of the tensor-core operand (the two differ by a random walk of roundings, ~2^-9 relative to a sum that is
+    itself a random walk), so it is held against the nearer of the two."""
+    g32 = nchw(dy_rows, n, h, w)
+    if z_rows is not None:
+        g32 = p.view(1, -1, 1, 1) * g32 + q.view(1, -1, 1, 1) * nchw(z_rows, n, h, w) + t.view(1, -1, 1, 1)
+    return min(rel_err(db, g32.sum((0, 2, 3))), rel_err(db, bfr(g32).sum((0, 2, 3))))
+
+
 def grad_operand(dy_rows, z_rows, n, h, w, p, q, t, rs=None):
     g = nchw(dy_rows, n, h, w)
     if rs is not None:
@@ -169,7 +179,7 @@ def test_wgrad3x3_vs_torch(lib, cin, cbuf, cout, n, h, w):
     g = grad_operand(dy, z, n, h, w, p_, q_, t_)
     ref = torch.nn.grad.conv2d_weight(a, (cout, cin, 3, 3), g, padding=1)
     assert rel_err(dw, ref) < DW_TOL
-    assert rel_err(db, g.sum((0, 2, 3))) < DW_TOL
+    assert db_err(db, dy, z, n, h, w, p_, q_, t_) < DW_TOL
 
 
 WG1 = [(24, 144, 2, 144, 144, False), (144, 40, 2, 144, 144, True), (240, 64, 3, 128, 112, True),
@@ -213,4 +223,4 @@ def test_wgradT_vs_torch(lib, cin, cout, n, h, w, bnz):
     g6 = g.view(n, cout, h, 2, w, 2)
     ref = torch.einsum("nihw,nohywx->ioyx", a, g6)
     assert rel_err(dw, ref) < DW_TOL
-    assert rel_err(db, g.sum((0, 2, 3))) < DW_TOL
+    assert db_err(db, dy, z if bnz else None, n, 2 * h, 2 * w, p_, q_, t_) < DW_TOL

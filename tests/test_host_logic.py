@@ -276,3 +276,34 @@ def test_two_rank_mosaic_assembly_gloo():
         ret = mgr.dict()
         mp.spawn(_mosaic_worker, args=(world, port, ret), nprocs=world, join=True)
         assert len(ret) == world and all(ret.values()), dict(ret)
+
+
+def test_fused_repack_table_stays_inside_every_pack():
+    """The fused Adam + re-pack pass scatters every parameter element to (row, tap, channel) of its packed copies by
+    peeling source strides (csrc/elementwise.cu pack_scatter).  Restated here on the entry table of a dry-run engine:
+    elements inside the packed slice land on distinct addresses inside the buffer, and elements outside it (the
+    data-gradient operand of the first decoder conv keeps 32 of the weight's 38 input channels) are skipped."""
+    from s2lc_b200._engine import Engine
+    model = _model("b0")
+    eng = Engine(model, dry_run=True)
+    eng.workspace(torch.zeros(2, 6, 128, 128), torch.bfloat16, True, True)
+    sliced = 0
+    for key, pw in eng.packs[torch.bfloat16].items():
+        e = pw.entry(pw.src.data_ptr())
+        n1, n2, taps, c = pw.geom[:4]
+        r = torch.arange(pw.src.numel())
+        idx = [torch.zeros_like(r) for _ in range(4)]
+        for d in range(4):
+            s = int(e.stride[d])
+            if s > 0:
+                q = r // s
+                idx[int(e.role[d])] = q
+                r = r - q * s
+        keep = (idx[1] < e.N2) & (idx[3] < e.Cpad)
+        sliced += int((~keep).any())
+        n = idx[0] * e.N2 + idx[1]
+        tap = (e.Tt - 1 - idx[2]) if e.flip else idx[2]
+        di = (n * e.Kpad + tap * e.Cpad + idx[3])[keep]
+        assert int(keep.sum()) == n1 * n2 * taps * c, key
+        assert int(di.max()) < pw.buf.numel() and di.unique().numel() == di.numel(), key
+    assert sliced >= 1
