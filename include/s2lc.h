@@ -277,6 +277,9 @@ int32_t s2lc_adam_pack_step(float* param, const float* grad, float* exp_avg, flo
  * took and that ran on the CUDA-core verification engine instead (include/s2lc.h top: the product path is tcgen05;
  * the count must stay 0 on the reference architectures — tests and bench.py assert / report it).  reset = 1 clears. */
 int64_t s2lc_simt_fallbacks(int32_t reset);
+/* Number of launches of the TMA-fed tcgen05 engine (csrc/tconv_tc.cu) since load; reset = 1 clears.  Tests use it to
+ * prove that a shape went through TMA rather than through one of the loader-warp engines. */
+int64_t s2lc_tma_launches(int32_t reset);
 /* SM count of the current device (sizes every persistent grid; read once from the driver, not a constant). */
 int32_t s2lc_num_sms(void);
 /* Test / profiling switches (bit 0: no streaming engines, 1: force the CUDA-core engine, 2: 7 producer warps,

@@ -94,6 +94,7 @@ _PROTOS = {
     "s2lc_adam_step": ([vp, vp, vp, vp, i64, f64, f64, f64, f64, f64, i64, f32, vp], i32),
     "s2lc_adam_pack_step": ([vp, vp, vp, vp, i64, f64, f64, f64, f64, f64, i64, f32, vp, i32, vp], i32),
     "s2lc_simt_fallbacks": ([i32], i64),
+    "s2lc_tma_launches": ([i32], i64),
     "s2lc_num_sms": ([], i32),
     "s2lc_set_debug_flags": ([C.c_uint32], C.c_uint32),
 }

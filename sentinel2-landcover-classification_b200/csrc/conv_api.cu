@@ -39,8 +39,10 @@ int32_t s2lc_conv_fwd(const s2lc_conv_params* p, void* stream) {
   A.stats = p->stats; A.stats_rowscale = p->stats_rowscale;
   cudaStream_t st = (cudaStream_t)stream;
   if (A.dtype == S2LC_BF16 && !force_simt()) {
-    int32_t r = launch_sconv_tc(A, st);
+    int32_t r = launch_tconv_tc(A, st);
     if (r <= 0) return r;  // taken (0) or error (<0)
+    r = launch_sconv_tc(A, st);
+    if (r <= 0) return r;
     r = launch_conv_tc(A, st);
     if (r <= 0) return r;
     note_simt_fallback();   // counted, never silent: s2lc_simt_fallbacks() must stay 0 on the reference architectures

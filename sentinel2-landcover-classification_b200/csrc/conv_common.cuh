@@ -167,9 +167,11 @@ __device__ __forceinline__ int64_t wgrad_index(const WgradArgs& P, int n, int k)
 }
 
 void note_simt_fallback();
+void note_tma_launch();
 int32_t launch_conv_simt(const ConvArgs& A, cudaStream_t st);
 int32_t launch_wgrad_simt(const WgradArgs& A, cudaStream_t st);
 int32_t launch_conv_tc(const ConvArgs& A, cudaStream_t st);      // igemm_tc.cu; returns 1 if shape not taken
+int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st);     // tconv_tc.cu (TMA-fed engine, plain operands); 1 if not taken
 int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st);     // sconv_tc.cu (streaming engine); returns 1 if shape not taken
 int32_t launch_wgrad_tc(const WgradArgs& A, cudaStream_t st);
 int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st);   // swgrad_tc.cu (streaming engine); 1 if shape not taken

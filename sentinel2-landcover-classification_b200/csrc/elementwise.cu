@@ -49,6 +49,7 @@ uint32_t debug_flags() {
     if ((e = getenv("S2LC_FORCE_SIMT")) && e[0] == '1') f |= DBG_FORCE_SIMT;
     if ((e = getenv("S2LC_SCONV_PROD")) && e[0] == '7') f |= DBG_SCONV_PROD7;
     if ((e = getenv("S2LC_NO_TMA")) && e[0] == '1') f |= DBG_NO_TMA;
+    if ((e = getenv("S2LC_TMA_ALL")) && e[0] == '1') f |= DBG_TMA_ALL;
     if ((e = getenv("S2LC_SWGRAD_LMAX")) && (atoi(e) == 64 || atoi(e) == 32)) f |= (uint32_t)atoi(e) << 8;
     g_dbg = f;
     g_dbg_init = true;
@@ -57,6 +58,8 @@ uint32_t debug_flags() {
 }
 static long long g_simt_fallbacks = 0;
 void note_simt_fallback() { __atomic_fetch_add(&g_simt_fallbacks, 1, __ATOMIC_RELAXED); }
+static long long g_tma_launches = 0;
+void note_tma_launch() { __atomic_fetch_add(&g_tma_launches, 1, __ATOMIC_RELAXED); }
 
 // Thread layout for [rows, C] tensors processed in 8-channel vectors.
 struct ChanIter {
@@ -1141,6 +1144,11 @@ int32_t s2lc_adam_step(float* param, const float* grad, float* exp_avg, float* e
 int64_t s2lc_simt_fallbacks(int32_t reset) {
   long long v = __atomic_load_n(&s2lc::g_simt_fallbacks, __ATOMIC_RELAXED);
   if (reset) __atomic_store_n(&s2lc::g_simt_fallbacks, 0, __ATOMIC_RELAXED);
+  return (int64_t)v;
+}
+int64_t s2lc_tma_launches(int32_t reset) {
+  long long v = __atomic_load_n(&s2lc::g_tma_launches, __ATOMIC_RELAXED);
+  if (reset) __atomic_store_n(&s2lc::g_tma_launches, 0, __ATOMIC_RELAXED);
   return (int64_t)v;
 }
 int32_t s2lc_num_sms(void) { return s2lc::num_sms(); }
