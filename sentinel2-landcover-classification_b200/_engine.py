@@ -24,6 +24,14 @@ from .efficientnet_unet import BlockSpec, EfficientnetUnet
 _DT = {torch.float32: L.F32, torch.bfloat16: L.BF16}
 # A/B switch for the decoder's materialised BatchNorm-backward gradients (see Workspace.materialize_grad)
 MATERIALIZE_DECODER_GRADS = os.environ.get("S2LC_MATERIALIZE", "1") != "0"
+# Operands of the compute-heavy contractions are written ONCE as plain bf16 tensors so that the TMA-fed engine
+# (csrc/tconv_tc.cu) takes them; S2LC_NO_TMA=1 keeps every operand lazy (the loader-warp engines, for A/B runs).
+TMA_OPERANDS = os.environ.get("S2LC_NO_TMA", "0") != "1"
+
+
+def tma_takes_3x3(width: int, c: int) -> bool:
+    """Mirror of the shape rule in csrc/tconv_tc.cu launch_tconv_tc."""
+    return width <= 128 or (width == 256 and c > 64)
 
 
 def _up(x: int, m: int) -> int:
@@ -228,6 +236,16 @@ class Workspace:
         self.B("s2lc_lazygrad_apply", C.byref(g), dy.data_ptr(), ld, rows, c, hw, self.dt, nbytes=3 * rows * c * self.es)
         return self.lazygrad(dy, ld)
 
+    def materialize_act(self, a: L.Lazy, rows: int, c: int, hw: int, desc: str = "") -> L.Lazy:
+        """act(BatchNorm(z)) (* squeeze-excite gate) written once as a plain bf16 tensor (s2lc_bn_apply): the operand
+        of a TMA-fed contraction in the forward pass and of its weight gradient in the backward pass."""
+        buf = self.act(rows, c)
+        self.F("s2lc_bn_apply", C.byref(a), None, 0, None, buf.data_ptr(), c, rows, c, hw, self.dt,
+               nbytes=2 * rows * c * self.es)
+        self.fwd_meta[-1][0] = "operand_apply"
+        self.fwd_meta[-1][3] = desc
+        return self.lazy(buf, c)
+
     def F(self, name: str, *args, nbytes: float = 0, flops: float = 0) -> None:
         self.fwd_list.append((getattr(self.lib, name), args))
         self.fwd_meta.append([name[5:], nbytes, flops, ""])
@@ -327,6 +345,7 @@ class Workspace:
         N, H, W, dt = self.N, self.H, self.W, self.dtype
         train, grad = self.training, self.need_grad
         nb = len(specs)
+        tma = TMA_OPERANDS and dt == torch.bfloat16
 
         def pk(key, factory):
             return eng.pack(dt, key, factory)
@@ -439,7 +458,11 @@ class Workspace:
             rec.z3 = self.act(rows_out, sp.c_out)
             rec.bn3 = _BN(self, bn3m, rows_out)
             rec.w3 = pack_1x1(rec.k3, conv3.weight)
-            self.conv(self.fwd_list, L.CONV_1X1, rec.s2_gated, N, ho, wo, sp.c_exp, rec.w3, rec.z3, sp.c_out,
+            # deep project convs (K >= 1056 at <= 32 px): the gated operand is written once and fed by TMA
+            rec.s2_op = rec.s2_gated
+            if tma and sp.c_exp >= 1056:
+                rec.s2_op = self.materialize_act(rec.s2_gated, rows_out, sp.c_exp, ho * wo, bd)
+            self.conv(self.fwd_list, L.CONV_1X1, rec.s2_op, N, ho, wo, sp.c_exp, rec.w3, rec.z3, sp.c_out,
                       stats=self.stats_f(rec.bn3), stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)
             self.bn_forward(rec.bn3)
             rec.Y = self.act(rows_out, sp.c_out)
@@ -494,7 +517,11 @@ class Workspace:
             lv.c_buf = _up(lv.c_cat, 8)
             lv.cat = self.act(lv.rows, lv.c_buf)
             lv.wup = pack_ct(lv.kup, up.weight)
-            self.conv(self.fwd_list, L.CONVT_FWD, dec_in, N, dec_h, dec_w, dec_in_c, lv.wup, lv.cat, lv.c_buf,
+            lv.in_op = dec_in
+            if tma and dec_in_c >= 128:
+                lv.in_op = self.materialize_act(dec_in, N * dec_h * dec_w, dec_in_c, dec_h * dec_w,
+                                                f"{N}x{dec_h}x{dec_w} C{dec_in_c} convT operand")
+            self.conv(self.fwd_list, L.CONVT_FWD, lv.in_op, N, dec_h, dec_w, dec_in_c, lv.wup, lv.cat, lv.c_buf,
                       bias=up.bias)
             if last:
                 self.F("s2lc_nchw_to_slice", self.x_ptr, lv.cat.data_ptr() + lv.c_up * self.es, lv.c_buf, N,
@@ -516,7 +543,10 @@ class Workspace:
                       stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)
             self.bn_forward(lv.bnA)
             lv.a1 = self.lazy(lv.zc1, co, lv.bnA.scale, lv.bnA.shift, act=L.ACT_RELU)
-            self.conv(self.fwd_list, L.CONV_3X3, lv.a1, N, lv.h, lv.w, co, lv.wB, lv.zc2, co, bias=dcv[3].bias,
+            lv.a1_op = lv.a1
+            if tma and tma_takes_3x3(lv.w, co):
+                lv.a1_op = self.materialize_act(lv.a1, lv.rows, co, lv.h * lv.w, f"{N}x{lv.h}x{lv.w} C{co} conv operand")
+            self.conv(self.fwd_list, L.CONV_3X3, lv.a1_op, N, lv.h, lv.w, co, lv.wB, lv.zc2, co, bias=dcv[3].bias,
                       stats=self.stats_f(lv.bnB), stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)
             self.bn_forward(lv.bnB)
             lv.a2 = self.lazy(lv.zc2, co, lv.bnB.scale, lv.bnB.shift, act=L.ACT_RELU)
@@ -573,7 +603,7 @@ class Workspace:
             gB = self.lazygrad(dyB, co, lv.zc2, co, lv.bnB)
             if MATERIALIZE_DECODER_GRADS:
                 gB = self.materialize_grad(gB, dyB, co, lv.rows, co, lv.h * lv.w)
-            self.wgrad(L.CONV_3X3, lv.a1, gB, N, lv.h, lv.w, co, co, self.gptr(lv.kdc + ".3.weight"),
+            self.wgrad(L.CONV_3X3, lv.a1_op, gB, N, lv.h, lv.w, co, co, self.gptr(lv.kdc + ".3.weight"),
                        self.gptr(lv.kdc + ".3.bias"))
             dyA = self.act(lv.rows, co)
             lv.dyA, lv.dyB = dyA, dyB
@@ -593,7 +623,7 @@ class Workspace:
             self.conv(self.bwd_list, L.CONV_3X3, gA, N, lv.h, lv.w, co, wA_d, lv.dcat, lv.c_dcat)
             # transposed conv: weight/bias gradient and data gradient into the level below
             gup = self.lazygrad(lv.dcat, lv.c_dcat)
-            self.wgrad(L.CONVT_FWD, lv.in_lazy, gup, N, lv.h_in, lv.w_in, lv.in_c, lv.c_up,
+            self.wgrad(L.CONVT_FWD, lv.in_op, gup, N, lv.h_in, lv.w_in, lv.in_c, lv.c_up,
                        self.gptr(lv.kup + ".weight"), self.gptr(lv.kup + ".bias"))
             wup_d = pack_ct_d(lv.kup, lv.up.weight)
             below = self.act(N * lv.h_in * lv.w_in, lv.in_c)
@@ -616,6 +646,7 @@ class Workspace:
         dY = [self.act(max_y, 1) for _ in range(2)]
         da_buf = self.act(max(r.rows_out * r.sp.c_exp for r in blocks), 1)
         dy1_buf = self.act(max(r.rows_in * r.sp.c_exp for r in blocks), 1)
+        g3m_buf = self.act(max(r.rows_out * r.sp.c_out for r in blocks), 1)
         se_scratch = self.f32(max(N * (r.sp.c_exp + 2 * r.sp.c_se) for r in blocks))
         dgate, dpool = self.f32(max(N * r.sp.c_exp for r in blocks)), self.f32(max(N * r.sp.c_exp for r in blocks))
 
@@ -639,7 +670,13 @@ class Workspace:
             bd = f"blk{i} {N}x{hi}x{wi} C{sp.c_exp} k{sp.kernel}s{sp.stride}"
             self.bn_backward(rec.bn3, rec.kbn3)
             g3 = self.lazygrad(dYi, sp.c_out, rec.z3, sp.c_out, rec.bn3, rowscale=dc_ptr(i))
-            self.wgrad(L.CONV_1X1, rec.s2_gated, g3, N, ho, wo, sp.c_exp, sp.c_out, self.gptr(rec.k3 + ".weight"))
+            if tma and sp.c_out >= 176:
+                # deep blocks: the BatchNorm-backward gradient is written once (out of place: dYi still feeds the
+                # residual path) and both gradient engines read it as a plain tensor, the data gradient through TMA
+                self.B("s2lc_lazygrad_apply", C.byref(g3), g3m_buf.data_ptr(), sp.c_out, rec.rows_out, sp.c_out,
+                       ho * wo, self.dt, nbytes=3 * rec.rows_out * sp.c_out * self.es)
+                g3 = self.lazygrad(g3m_buf, sp.c_out)
+            self.wgrad(L.CONV_1X1, rec.s2_op, g3, N, ho, wo, sp.c_exp, sp.c_out, self.gptr(rec.k3 + ".weight"))
             w3_d = pack_1x1_d(rec.k3, enc.blocks[i].final_layer[0].weight)
             self.conv(self.bwd_list, L.CONV_1X1, g3, N, ho, wo, sp.c_out, w3_d, da_buf, sp.c_exp)
             # squeeze-excite backward
@@ -669,6 +706,8 @@ class Workspace:
                 self.meta(self.bwd_meta, dw_bytes, dw_flops, desc=bd)
                 self.bn_backward(rec.bn1, rec.kbn1)
                 g1 = self.lazygrad(dy1_buf, sp.c_exp, rec.z1, sp.c_exp, rec.bn1)
+                if tma and sp.c_exp >= 1056:
+                    g1 = self.materialize_grad(g1, dy1_buf, sp.c_exp, rec.rows_in, sp.c_exp, hi * wi)
                 self.wgrad(L.CONV_1X1, rec.x_lazy, g1, N, hi, wi, sp.c_in, sp.c_exp, self.gptr(rec.k1 + ".weight"))
                 if prev_rec is None:
                     raise RuntimeError("block 0 with an expand conv is not a reference architecture")

@@ -190,6 +190,12 @@ __global__ void bn_apply_kernel(s2lc_lazy in, const T* __restrict__ res, int64_t
       float rs = rowscale ? rowscale[r / HW] : 1.f;
 #pragma unroll
       for (int j = 0; j < 8; ++j) v[j] = act_fwd_t<T>(v[j] * sc[j] + sh[j], in.act) * rs;
+      if (in.gate) {   // squeeze-excite gate [N, C]: the materialised operand of a project conv
+        float g[8];
+        Vec8<float>::load(in.gate + (r / HW) * C + cv * 8, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= g[j];
+      }
       if (res) {
         float e[8];
         Vec8<T>::load(res + r * ld_res + cv * 8, e);

@@ -439,10 +439,17 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
   K.taps = A.mode == S2LC_CONV_3X3 ? 9 : 1;
   K.KC = (A.C + 63) / 64;
   K.ksteps_last = (A.C - (K.KC - 1) * 64 + 15) / 16;
+  // Which plain shapes this engine takes (tools/tma_sweep.sh, profiles/r02b_tma_sweep.txt): 3x3 layers up to 128 px
+  // wide rows, and 256 px rows with more than one 64-channel chunk (wider / thinner ones are HBM-bound and belong to
+  // the rolling-row engine, sconv_tc.cu); 1x1 and transposed convs from 176 / 128 input channels (below that the
+  // tile is all epilogue and the 12-epilogue-warp streaming engine is as fast or faster).
+  const bool take_all = (dbg & DBG_TMA_ALL) != 0;
+  if (!take_all) {
+    if (A.mode == S2LC_CONV_1X1 && A.C < 176) return 1;
+    if (A.mode == S2LC_CONVT_FWD && A.C < 128) return 1;
+  }
   if (K.taps == 9) {
-    // rows wider than 128 px with <= 128 channels are HBM-bound and belong to the rolling-row engine (sconv_tc.cu)
-    const bool take_all = (dbg & DBG_TMA_ALL) != 0;
-    if (A.W > 128 && !take_all) return 1;
+    if (!take_all && !(A.W <= 128 || (A.W == 256 && A.C > 64))) return 1;
     K.bw = A.W < 128 ? A.W : 128;
     if ((K.bw & (K.bw - 1)) != 0 || K.bw < 8 || A.W % K.bw != 0) return 1;
     K.bh = 128 / K.bw;

@@ -17,6 +17,16 @@ BF = torch.bfloat16
 OUT_TOL = 4e-3
 
 
+@pytest.fixture(autouse=True)
+def take_all_shapes(lib):
+    """The dispatcher hands the TMA engine only the shapes it wins on (csrc/tconv_tc.cu); the tests also cover the
+    thin ones it leaves to the streaming engine in production (debug flag bit 4 = take every plain shape)."""
+    old = lib.s2lc_set_debug_flags(0)
+    lib.s2lc_set_debug_flags((old | 16) & ~(1 | 2 | 8))
+    yield
+    lib.s2lc_set_debug_flags(old)
+
+
 def took_tma(lib, fn):
     lib.s2lc_tma_launches(1)
     fn()
