@@ -356,36 +356,39 @@ __global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_laz
 // 256 of the C channels.
 constexpr int SE_CB = 256;
 
-// hidden pre-activation hp[s] = W1[s, :] . x + b1[s] for one sample (x in smem), all warps of the block
-__device__ __forceinline__ void se_hidden(const float* xs, const float* __restrict__ w1, const float* __restrict__ b1,
-                                          float* hp, int C, int S) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  for (int s = warp; s < S; s += nw) {
-    const float* wr = w1 + (int64_t)s * C;
-    float a = 0.f;
-    for (int c = lane * 4; c + 3 < C; c += 128) {
-      const float4 w = __ldg(reinterpret_cast<const float4*>(wr + c));
-      a += w.x * xs[c] + w.y * xs[c + 1] + w.z * xs[c + 2] + w.w * xs[c + 3];
-    }
-    a = warp_sum(a);
-    if (lane == 0) hp[s] = a + b1[s];
+// Hidden pre-activations hp[n, s] = W1[s, :] . pooled[n, :] + b1[s] for ALL samples, one warp per (s, n): grid
+// (ceil(S / 8), N).  Its own launch because every (channel block, sample) CTA of the gate kernels used to recompute all
+// S hidden units of its sample — C/256 times the W1 traffic (12 x 1.5 MB per sample at C = 3072), which set the time of
+// the deep blocks (0.15 ms per forward call, 0.22 ms per backward call).  `zero` (optional, [N, S]) is cleared for the
+// backward accumulation that follows.
+__global__ void __launch_bounds__(256) se_hidden_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
+                                                        const float* __restrict__ b1, float* __restrict__ hp,
+                                                        float* __restrict__ zero, int C, int S) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.y, s = blockIdx.x * 8 + warp;
+  if (s >= S) return;
+  const float4* wr = reinterpret_cast<const float4*>(w1 + (int64_t)s * C);
+  const float4* xr = reinterpret_cast<const float4*>(pooled + (int64_t)n * C);
+  float a = 0.f;
+  for (int c4 = lane; c4 < C / 4; c4 += 32) {
+    const float4 w = __ldg(wr + c4), x = __ldg(xr + c4);
+    a += w.x * x.x + w.y * x.y + w.z * x.z + w.w * x.w;
+  }
+  a = warp_sum(a);
+  if (lane == 0) {
+    hp[(int64_t)n * S + s] = a + b1[s];
+    if (zero) zero[(int64_t)n * S + s] = 0.f;
   }
 }
 
-// gate = sigmoid(W2 silu(W1 pooled + b1) + b2)
-__global__ void __launch_bounds__(256) se_fc_fwd_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
-                                                        const float* __restrict__ b1, const float* __restrict__ w2,
+// gate = sigmoid(W2 silu(hp) + b2), grid (channel blocks of 256, N)
+__global__ void __launch_bounds__(256) se_fc_fwd_kernel(const float* __restrict__ hp, const float* __restrict__ w2,
                                                         const float* __restrict__ b2, float* __restrict__ gate, int C,
                                                         int S) {
   extern __shared__ float smem[];
-  float* xs = smem;      // [C]
-  float* hs = smem + C;  // [S]
+  float* hs = smem;  // [S]
   const int n = blockIdx.y, c = blockIdx.x * SE_CB + threadIdx.x;
-  for (int i = threadIdx.x; i < C; i += blockDim.x) xs[i] = pooled[(int64_t)n * C + i];
-  __syncthreads();
-  se_hidden(xs, w1, b1, hs, C, S);
-  __syncthreads();
-  for (int s = threadIdx.x; s < S; s += blockDim.x) hs[s] = act_fwd(hs[s], S2LC_ACT_SILU);
+  for (int s = threadIdx.x; s < S; s += blockDim.x) hs[s] = act_fwd(hp[(int64_t)n * S + s], S2LC_ACT_SILU);
   __syncthreads();
   if (c < C) {
     float a = b2[c];
@@ -395,28 +398,18 @@ __global__ void __launch_bounds__(256) se_fc_fwd_kernel(const float* __restrict_
   }
 }
 
-// backward, step 1: dgp[n, c] = dgate * g(1-g); hp[n, s] (pre-activation, written by channel block 0);
-// dacc[n, s] += sum over this block's channels of dgp[c] * W2[c, s]   (dacc pre-zeroed)
-__global__ void __launch_bounds__(256) se_fc_bwd1_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
-                                                         const float* __restrict__ b1, const float* __restrict__ w2,
-                                                         const float* __restrict__ b2, const float* __restrict__ dgate,
-                                                         float* __restrict__ sc_dgp, float* __restrict__ sc_hp,
-                                                         float* __restrict__ sc_dacc, int C, int S) {
+// backward, step 1: dgp[n, c] = dgate * g(1-g);
+// dacc[n, s] += sum over this block's channels of dgp[c] * W2[c, s]   (dacc zeroed by se_hidden_kernel)
+__global__ void __launch_bounds__(256) se_fc_bwd1_kernel(const float* __restrict__ w2, const float* __restrict__ b2,
+                                                         const float* __restrict__ dgate, float* __restrict__ sc_dgp,
+                                                         const float* __restrict__ sc_hp, float* __restrict__ sc_dacc,
+                                                         int C, int S) {
   extern __shared__ float smem[];
-  float* xs = smem;               // [C]
-  float* hp = smem + C;           // [S] pre-activation
-  float* hs = hp + S;             // [S] silu(hp)
+  float* hs = smem;               // [S] silu(hp)
   float* dg = hs + S;             // [SE_CB]
   const int n = blockIdx.y, c0 = blockIdx.x * SE_CB, c = c0 + threadIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  for (int i = threadIdx.x; i < C; i += blockDim.x) xs[i] = pooled[(int64_t)n * C + i];
-  __syncthreads();
-  se_hidden(xs, w1, b1, hp, C, S);
-  __syncthreads();
-  for (int s = threadIdx.x; s < S; s += blockDim.x) {
-    hs[s] = act_fwd(hp[s], S2LC_ACT_SILU);
-    if (blockIdx.x == 0) sc_hp[(int64_t)n * S + s] = hp[s];
-  }
+  for (int s = threadIdx.x; s < S; s += blockDim.x) hs[s] = act_fwd(sc_hp[(int64_t)n * S + s], S2LC_ACT_SILU);
   __syncthreads();
   float d = 0.f;
   if (c < C) {
@@ -1028,12 +1021,33 @@ int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, f
   return check_launch("se_bwd_reduce");
 }
 
+// library-owned [N, S] scratch of the forward hidden pre-activations (one stream per process launches these kernels)
+static float* g_se_hp[64];
+static size_t g_se_hp_floats[64];
+static int32_t se_hp_scratch(size_t floats, float** out) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("se hidden scratch: bad device"); return S2LC_ERR_CUDA; }
+  if (floats > g_se_hp_floats[dev]) {
+    if (g_se_hp[dev]) cudaFree(g_se_hp[dev]);
+    g_se_hp_floats[dev] = floats < 16384 ? 16384 : 2 * floats;
+    if (cudaMalloc(&g_se_hp[dev], g_se_hp_floats[dev] * sizeof(float)) != cudaSuccess) {
+      g_se_hp[dev] = nullptr; g_se_hp_floats[dev] = 0; set_error("se hidden scratch: cudaMalloc"); return S2LC_ERR_CUDA;
+    }
+  }
+  *out = g_se_hp[dev];
+  return S2LC_OK;
+}
+
 int32_t s2lc_se_fc_fwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                        float* gate, int32_t N, int32_t C, int32_t S, void* stream) {
   S2LC_REQUIRE(C % 4 == 0, S2LC_ERR_ALIGN, "se_fc_fwd: C=%d must be a multiple of 4", C);
-  size_t smem = sizeof(float) * (size_t)(C + S);
+  float* hp;
+  int32_t rc = se_hp_scratch((size_t)N * S, &hp);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  se_hidden_kernel<<<dim3((S + 7) / 8, N), 256, 0, st>>>(pooled, w1, b1, hp, nullptr, C, S);
   dim3 grid((C + SE_CB - 1) / SE_CB, N);
-  se_fc_fwd_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(pooled, w1, b1, w2, b2, gate, C, S);
+  se_fc_fwd_kernel<<<grid, 256, sizeof(float) * (size_t)S, st>>>(hp, w2, b2, gate, C, S);
   return check_launch("se_fc_fwd");
 }
 
@@ -1045,14 +1059,9 @@ int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, co
   float* sc_hp = scratch + (size_t)N * C;        // [N, S] hidden pre-activation
   float* sc_dacc = sc_hp + (size_t)N * S;        // [N, S] sum_c dgp * W2 (accumulated atomically)
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(sc_dacc, 0, sizeof(float) * (size_t)N * S, st);
-  if (e != cudaSuccess) {
-    set_error("se_fc_bwd: memset: %s", cudaGetErrorString(e));
-    return S2LC_ERR_CUDA;
-  }
+  se_hidden_kernel<<<dim3((S + 7) / 8, N), 256, 0, st>>>(pooled, w1, b1, sc_hp, sc_dacc, C, S);
   dim3 grid((C + SE_CB - 1) / SE_CB, N);
-  se_fc_bwd1_kernel<<<grid, 256, sizeof(float) * (size_t)(C + 2 * S + SE_CB), st>>>(pooled, w1, b1, w2, b2, dgate,
-                                                                                    sc_dgp, sc_hp, sc_dacc, C, S);
+  se_fc_bwd1_kernel<<<grid, 256, sizeof(float) * (size_t)(S + SE_CB), st>>>(w2, b2, dgate, sc_dgp, sc_hp, sc_dacc, C, S);
   se_fc_bwd2_kernel<<<grid, 256, sizeof(float) * (size_t)S, st>>>(w1, sc_hp, sc_dacc, dpool, C, S);
   se_fc_bwd_weight_kernel<<<(C * S + 255) / 256, 256, 0, st>>>(pooled, sc_dgp, sc_hp, sc_dacc, dw1, db1, dw2, db2, N,
                                                                 C, S);

@@ -13,8 +13,8 @@
 //        (kc*64, x0+dx-1, y0+dy-1, n) — im2col by shifted boxes, zero padding = TMA out-of-bounds fill; 1x1 and
 //        transposed convs use a 2-D map (C, M).  SWIZZLE_128B, so the box lands as the K-major tile UMMA reads.
 //   * B: one 2-D map over the packed weights [Npad, Kpad], box (64, BN).
-// Roles (10 warps, one CTA per SM, static tile schedule): warp 0 = TMA producer (one lane), warp 1 = MMA issuer (one
-// lane; owns TMEM), warps 2-9 = epilogue (two warps per TMEM lane quarter, alternating 16-column chunks): tcgen05.ld ->
+// Roles (14 warps, one CTA per SM, static tile schedule): warp 0 = TMA producer (one lane), warp 1 = MMA issuer (one
+// lane; owns TMEM), warps 2-13 = epilogue (three warps per TMEM lane quarter, interleaved 16-column chunks): tcgen05.ld ->
 // bias, residuals, act'(prev), bf16 16 B stores (incl. the 2x2 scatter of the transposed conv), BatchNorm moments.
 // Two TMEM accumulators: the epilogue of tile i overlaps the main loop of tile i+1.
 #include <cuda.h>
@@ -28,7 +28,7 @@ namespace s2lc {
 
 using namespace tc;
 
-constexpr int TV_EPI_WARPS = 8;
+constexpr int TV_EPI_WARPS = 12;
 constexpr int TV_WARPS = 2 + TV_EPI_WARPS;
 constexpr int TV_THREADS = TV_WARPS * 32;
 constexpr int TV_MAX_STAGES = 8;
@@ -95,8 +95,12 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  float* sstat = reinterpret_cast<float*>(smem + K.stages * K.stage_bytes);   // [2 accumulators][2][256]
-  uint64_t* full = reinterpret_cast<uint64_t*>(sstat + 2 * 512);
+  // per-channel statistics of ALL column tiles this CTA visits, [2][n_tiles * BN] floats, flushed once at the end
+  // (a flush per tile is two fp64 atomics per column from every CTA on the same addresses: on the thin layers —
+  // 16 k tiles of 128 x 144 — the L2 atomic unit, not the tensor core, set the pace)
+  float* sstat = reinterpret_cast<float*>(smem + K.stages * K.stage_bytes);
+  const int NS = K.n_tiles * K.BN;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sstat + 2 * NS);
   uint64_t* empty = full + TV_MAX_STAGES;
   uint64_t* acc_full = empty + TV_MAX_STAGES;
   uint64_t* acc_empty = acc_full + 2;
@@ -113,7 +117,7 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
     tma_prefetch_desc(&tmB);
   }
   if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)K.tmem_cols);
-  for (int i = tid; i < 2 * 512; i += TV_THREADS) sstat[i] = 0.f;
+  for (int i = tid; i < 2 * NS; i += TV_THREADS) sstat[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -181,8 +185,8 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
     }
   } else {
     // ================================================================== epilogue
-    const int ew = warp - 2, q = warp & 3, half = ew >> 2;     // q = TMEM lane quarter this warp may read
-    const int etid = ew * 32 + lane;                            // 0..255 among the epilogue threads
+    constexpr int NSUB = TV_EPI_WARPS / 4;                      // warps per TMEM lane quarter
+    const int ew = warp - 2, q = warp & 3, sub = ew >> 2;       // q = TMEM lane quarter this warp may read
     const int r = q * 32 + lane;                                // accumulator row = pixel of the tile
     bf16* outp = reinterpret_cast<bf16*>(P.out);
     const bf16* prevp = P.has_prev ? reinterpret_cast<const bf16*>(P.prev.raw) : nullptr;
@@ -193,6 +197,13 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
     const int stats_kind = P.stats_kind;
     const int nchunks = K.BN / 16;
     const int hw = P.H * P.W;
+    // global operands of one 16-column chunk of this thread's row, fetched ONE CHUNK AHEAD of their use (and, for the
+    // first chunk of a tile, before the wait for the accumulator): a 16 B load per row and tensor is all latency
+    struct Ops {
+      uint4 pz0, pz1, ra0, ra1, rb0, rb1;
+      int64_t orow;
+      int col0, nvalid;
+    };
     int b = 0;
     uint32_t bph = 0;
     for (int t = blockIdx.x; t < K.total_tiles; t += gridDim.x) {
@@ -216,71 +227,87 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
         ph_ = rem / P.W;
         pw_ = rem - ph_ * P.W;
       }
-      const float srs = (stats_kind == S2LC_STATS_BNBWD && P.stats_rowscale) ? __ldg(P.stats_rowscale + sn) : 1.f;
-      float* gstat = sstat + b * 512;
-      mbar_wait(&acc_full[b], bph);
-      tc_fence_after();
-      for (int cj = half; cj < nchunks; cj += 2) {
+      auto fetch = [&](int cj, Ops& o) {
         const int ncol0 = n0 + cj * 16;
-        int nvalid = P.Nout - ncol0;
-        if (nvalid <= 0) break;                                 // warp-uniform
-        nvalid = nvalid > 16 ? 16 : nvalid;
-        const bool fullc = nvalid == 16;
-        int col0 = ncol0;
-        int64_t orow = m;
+        int nv = P.Nout - ncol0;
+        o.nvalid = nv > 16 ? 16 : nv;
+        o.col0 = ncol0;
+        o.orow = m;
         if (P.mode == S2LC_CONVT_FWD) {
           const int qq = ncol0 / P.Cout;
-          col0 = ncol0 - qq * P.Cout;
-          orow = ((int64_t)sn * (2 * P.H) + 2 * ph_ + (qq >> 1)) * (2 * P.W) + 2 * pw_ + (qq & 1);
+          o.col0 = ncol0 - qq * P.Cout;
+          o.orow = ((int64_t)sn * (2 * P.H) + 2 * ph_ + (qq >> 1)) * (2 * P.W) + 2 * pw_ + (qq & 1);
         }
-        // global operands of this chunk first, then the accumulator
-        uint4 pz0 = make_uint4(0, 0, 0, 0), pz1 = pz0, ra0 = pz0, ra1 = pz0, rb0 = pz0, rb1 = pz0;
-        if (valid && fullc) {
+        o.pz0 = make_uint4(0, 0, 0, 0);
+        o.pz1 = o.pz0; o.ra0 = o.pz0; o.ra1 = o.pz0; o.rb0 = o.pz0; o.rb1 = o.pz0;
+        if (valid && o.nvalid == 16) {
           if (prevp) {
-            const uint4* p = reinterpret_cast<const uint4*>(prevp + orow * P.prev.ld + col0);
-            pz0 = __ldg(p); pz1 = __ldg(p + 1);
+            const uint4* p = reinterpret_cast<const uint4*>(prevp + o.orow * P.prev.ld + o.col0);
+            o.pz0 = __ldg(p); o.pz1 = __ldg(p + 1);
           }
           if (res1p) {
-            const uint4* p = reinterpret_cast<const uint4*>(res1p + orow * P.ld_res1 + col0);
-            ra0 = __ldg(p); ra1 = __ldg(p + 1);
+            const uint4* p = reinterpret_cast<const uint4*>(res1p + o.orow * P.ld_res1 + o.col0);
+            o.ra0 = __ldg(p); o.ra1 = __ldg(p + 1);
           }
           if (res2p) {
-            const uint4* p = reinterpret_cast<const uint4*>(res2p + orow * P.ld_res2 + col0);
-            rb0 = __ldg(p); rb1 = __ldg(p + 1);
+            const uint4* p = reinterpret_cast<const uint4*>(res2p + o.orow * P.ld_res2 + o.col0);
+            o.rb0 = __ldg(p); o.rb1 = __ldg(p + 1);
           }
         }
+      };
+      const float srs = (stats_kind == S2LC_STATS_BNBWD && P.stats_rowscale) ? __ldg(P.stats_rowscale + sn) : 1.f;
+      float* gstat = sstat + n0;
+      Ops cur, nxt;
+      if (sub < nchunks) fetch(sub, cur);
+      mbar_wait(&acc_full[b], bph);
+      tc_fence_after();
+      for (int cj = sub; cj < nchunks; cj += NSUB) {
+        if (cur.nvalid <= 0) break;                             // warp-uniform: columns beyond Nout
+        if (cj + NSUB < nchunks) fetch(cj + NSUB, nxt);
+        const int nvalid = cur.nvalid, col0 = cur.col0;
+        const int64_t orow = cur.orow;
+        const bool fullc = nvalid == 16;
         float acc[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * K.BN + cj * 16), acc);
         float zp[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) zp[j] = 0.f;
         if (P.bias) {
+          if (fullc) {
+            const float4* bv = reinterpret_cast<const float4*>(P.bias + col0);
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j < nvalid) acc[j] += __ldg(P.bias + col0 + j);
+            for (int j4 = 0; j4 < 4; ++j4) {
+              const float4 tb = __ldg(bv + j4);
+              acc[4 * j4] += tb.x; acc[4 * j4 + 1] += tb.y; acc[4 * j4 + 2] += tb.z; acc[4 * j4 + 3] += tb.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (j < nvalid) acc[j] += __ldg(P.bias + col0 + j);
+          }
         }
         if (valid) {
           if (fullc) {
             float e[8];
             if (res1p) {
-              sc_unpack8(ra0, e);
+              sc_unpack8(cur.ra0, e);
 #pragma unroll
               for (int j = 0; j < 8; ++j) acc[j] += e[j];
-              sc_unpack8(ra1, e);
+              sc_unpack8(cur.ra1, e);
 #pragma unroll
               for (int j = 0; j < 8; ++j) acc[8 + j] += e[j];
             }
             if (res2p) {
-              sc_unpack8(rb0, e);
+              sc_unpack8(cur.rb0, e);
 #pragma unroll
               for (int j = 0; j < 8; ++j) acc[j] += e[j];
-              sc_unpack8(rb1, e);
+              sc_unpack8(cur.rb1, e);
 #pragma unroll
               for (int j = 0; j < 8; ++j) acc[8 + j] += e[j];
             }
             if (prevp) {
-              sc_unpack8(pz0, *reinterpret_cast<float(*)[8]>(&zp[0]));
-              sc_unpack8(pz1, *reinterpret_cast<float(*)[8]>(&zp[8]));
+              sc_unpack8(cur.pz0, *reinterpret_cast<float(*)[8]>(&zp[0]));
+              sc_unpack8(cur.pz1, *reinterpret_cast<float(*)[8]>(&zp[8]));
             }
           } else {
 #pragma unroll
@@ -293,13 +320,31 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
             }
           }
           if (prev_act != S2LC_ACT_NONE) {
+            float u[16];
+            if (prev_aff && fullc) {
+              const float4* sv = reinterpret_cast<const float4*>(P.prev.scale + col0);
+              const float4* hv = reinterpret_cast<const float4*>(P.prev.shift + col0);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (j < nvalid) {
-                float u = zp[j];
-                if (prev_aff) u = fmaf(u, __ldg(P.prev.scale + col0 + j), __ldg(P.prev.shift + col0 + j));
-                acc[j] = prev_act == S2LC_ACT_RELU ? (u > 0.f ? acc[j] : 0.f) : acc[j] * act_bwd_fast(u, S2LC_ACT_SILU);
+              for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 a4 = __ldg(sv + j4), b4 = __ldg(hv + j4);
+                u[4 * j4] = fmaf(zp[4 * j4], a4.x, b4.x);
+                u[4 * j4 + 1] = fmaf(zp[4 * j4 + 1], a4.y, b4.y);
+                u[4 * j4 + 2] = fmaf(zp[4 * j4 + 2], a4.z, b4.z);
+                u[4 * j4 + 3] = fmaf(zp[4 * j4 + 3], a4.w, b4.w);
               }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                u[j] = zp[j];
+                if (prev_aff && j < nvalid) u[j] = fmaf(zp[j], __ldg(P.prev.scale + col0 + j), __ldg(P.prev.shift + col0 + j));
+              }
+            }
+            if (prev_act == S2LC_ACT_RELU) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) acc[j] = u[j] > 0.f ? acc[j] : 0.f;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) acc[j] *= act_bwd_fast(u[j], S2LC_ACT_SILU);
             }
           }
         }
@@ -344,33 +389,29 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
           const float t1 = sc_butterfly16(s1, lane, col);
           if ((lane & 1) == 0) {
             atomicAdd(&gstat[cj * 16 + col], t0);
-            atomicAdd(&gstat[256 + cj * 16 + col], t1);
+            atomicAdd(&gstat[NS + cj * 16 + col], t1);
           }
         }
+        cur = nxt;
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) sc_mbar_arrive(&acc_empty[b]);
-      if (stats_kind != S2LC_STATS_NONE) {
-        // all eight epilogue warps have added their column sums of this tile: flush them (double-buffered by
-        // accumulator, so the next tile's sums never meet this flush)
-        asm volatile("bar.sync 1, %0;" ::"n"(TV_EPI_WARPS * 32) : "memory");
-        for (int i = etid; i < K.BN; i += TV_EPI_WARPS * 32) {
-          const float v0 = gstat[i], v1 = gstat[256 + i];
-          if (n0 + i < P.Nout) {
-            atomicAdd(&P.stats[n0 + i], (double)v0);
-            atomicAdd(&P.stats[P.Nout + n0 + i], (double)v1);
-          }
-          gstat[i] = 0.f;
-          gstat[256 + i] = 0.f;
-        }
-      }
       if (++b == 2) { b = 0; bph ^= 1u; }
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)K.tmem_cols);
+  if (P.stats_kind != S2LC_STATS_NONE) {
+    for (int i = tid; i < NS; i += TV_THREADS) {
+      const float v0 = sstat[i], v1 = sstat[NS + i];
+      if (i < P.Nout && (v0 != 0.f || v1 != 0.f)) {
+        atomicAdd(&P.stats[i], (double)v0);
+        atomicAdd(&P.stats[P.Nout + i], (double)v1);
+      }
+    }
+  }
 }
 
 // ---- host side --------------------------------------------------------------------------------------------------
@@ -471,7 +512,7 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
   K.n_tiles = (A.Nout + K.BN - 1) / K.BN;
   K.total_tiles = K.m_tiles * K.n_tiles;
   K.stage_bytes = TV_A_BYTES + K.BN * 128;
-  const int fixed = 1024 + 2 * 512 * 4 + (2 * TV_MAX_STAGES + 4) * 8 + 64;
+  const int fixed = 1024 + 2 * K.n_tiles * K.BN * 4 + (2 * TV_MAX_STAGES + 4) * 8 + 64;
   K.stages = (226 * 1024 - fixed) / K.stage_bytes;
   if (K.stages > TV_MAX_STAGES) K.stages = TV_MAX_STAGES;
   if (K.stages < 2) return 1;
