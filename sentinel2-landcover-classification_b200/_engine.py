@@ -458,9 +458,9 @@ class Workspace:
             rec.z3 = self.act(rows_out, sp.c_out)
             rec.bn3 = _BN(self, bn3m, rows_out)
             rec.w3 = pack_1x1(rec.k3, conv3.weight)
-            # deep project convs (K >= 1056 at <= 32 px): the gated operand is written once and fed by TMA
+            # project convs at <= 64 px: the gated operand is written once and fed by TMA (forward conv + weight gradient)
             rec.s2_op = rec.s2_gated
-            if tma and sp.c_exp >= 1056:
+            if tma and ho * wo <= 64 * 64:
                 rec.s2_op = self.materialize_act(rec.s2_gated, rows_out, sp.c_exp, ho * wo, bd)
             self.conv(self.fwd_list, L.CONV_1X1, rec.s2_op, N, ho, wo, sp.c_exp, rec.w3, rec.z3, sp.c_out,
                       stats=self.stats_f(rec.bn3), stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)
@@ -670,7 +670,7 @@ class Workspace:
             bd = f"blk{i} {N}x{hi}x{wi} C{sp.c_exp} k{sp.kernel}s{sp.stride}"
             self.bn_backward(rec.bn3, rec.kbn3)
             g3 = self.lazygrad(dYi, sp.c_out, rec.z3, sp.c_out, rec.bn3, rowscale=dc_ptr(i))
-            if tma and sp.c_out >= 176:
+            if tma and ho * wo <= 64 * 64:
                 # deep blocks: the BatchNorm-backward gradient is written once (out of place: dYi still feeds the
                 # residual path) and both gradient engines read it as a plain tensor, the data gradient through TMA
                 self.B("s2lc_lazygrad_apply", C.byref(g3), g3m_buf.data_ptr(), sp.c_out, rec.rows_out, sp.c_out,
@@ -706,7 +706,7 @@ class Workspace:
                 self.meta(self.bwd_meta, dw_bytes, dw_flops, desc=bd)
                 self.bn_backward(rec.bn1, rec.kbn1)
                 g1 = self.lazygrad(dy1_buf, sp.c_exp, rec.z1, sp.c_exp, rec.bn1)
-                if tma and sp.c_exp >= 1056:
+                if tma and hi * wi <= 64 * 64:
                     g1 = self.materialize_grad(g1, dy1_buf, sp.c_exp, rec.rows_in, sp.c_exp, hi * wi)
                 self.wgrad(L.CONV_1X1, rec.x_lazy, g1, N, hi, wi, sp.c_in, sp.c_exp, self.gptr(rec.k1 + ".weight"))
                 if prev_rec is None:

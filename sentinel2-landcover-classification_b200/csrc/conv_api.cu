@@ -61,7 +61,9 @@ int32_t s2lc_conv_wgrad(const s2lc_wgrad_params* p, void* stream) {
   A.a = *p->a; A.g = *p->g; A.dw = p->dw; A.dbias = p->dbias;
   cudaStream_t st = (cudaStream_t)stream;
   if (A.dtype == S2LC_BF16 && !force_simt()) {
-    int32_t r = launch_swgrad_tc(A, st);
+    int32_t r = launch_twgrad_tc(A, st);
+    if (r <= 0) return r;
+    r = launch_swgrad_tc(A, st);
     if (r <= 0) return r;
     r = launch_wgrad_tc(A, st);
     if (r <= 0) return r;

@@ -174,6 +174,7 @@ int32_t launch_conv_tc(const ConvArgs& A, cudaStream_t st);      // igemm_tc.cu;
 int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st);     // tconv_tc.cu (TMA-fed engine, plain operands); 1 if not taken
 int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st);     // sconv_tc.cu (streaming engine); returns 1 if shape not taken
 int32_t launch_wgrad_tc(const WgradArgs& A, cudaStream_t st);
+int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st);   // twgrad_tc.cu (TMA-fed engine, plain operands, deep layers)
 int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st);   // swgrad_tc.cu (streaming engine); 1 if shape not taken
 
 }  // namespace s2lc

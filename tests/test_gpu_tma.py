@@ -120,3 +120,55 @@ def test_tma_convT(lib, cin, cout, n, h, w):
     got = nchw(cat, n, 2 * h, 2 * w)
     assert rel_err(got[:, :cout], ref) < OUT_TOL
     assert float(got[:, cout:].abs().max()) == 0.0
+
+
+# ------------------------------------------------------------------------------------------ weight gradients (twgrad_tc.cu)
+from test_gpu_kernels import run_wgrad  # noqa: E402
+
+DW_TOL = 1e-3
+
+W3 = [(640, 512, 2, 32, 32), (512, 512, 1, 32, 32), (320, 256, 2, 64, 64), (256, 256, 1, 40, 64), (40, 32, 3, 16, 16),
+      (72, 200, 2, 8, 16), (168, 128, 1, 24, 128)]
+
+
+@pytest.mark.parametrize("cin,cout,n,h,w", W3)
+def test_tma_wgrad3x3(lib, cin, cout, n, h, w):
+    rows = n * h * w
+    x = mk((rows, cin), 341).to(BF)
+    g = mk((rows, cout), 342).to(BF)
+    dw = torch.zeros(cout, cin, 3, 3, device="cuda")
+    db = torch.zeros(cout, device="cuda")
+    took_tma(lib, lambda: run_wgrad(lib, 1, 1, lazy(x, cin), lazygrad(g, cout), n, h, w, cin, cout, dw, db))
+    ref = torch.nn.grad.conv2d_weight(nchw(x, n, h, w), (cout, cin, 3, 3), nchw(g, n, h, w), padding=1)
+    assert rel_err(dw, ref) < DW_TOL
+    assert rel_err(db, nchw(g, n, h, w).sum((0, 2, 3))) < DW_TOL
+
+
+W1 = [(304, 1824, 16, 16, 16), (1824, 304, 16, 16, 16), (176, 1056, 8, 32, 32), (512, 2048, 4, 16, 16),
+      (128, 768, 4, 32, 32), (40, 240, 3, 50, 30), (1056, 176, 2, 9, 9)]
+
+
+@pytest.mark.parametrize("cin,cout,n,h,w", W1)
+def test_tma_wgrad1x1(lib, cin, cout, n, h, w):
+    rows = n * h * w
+    x = mk((rows, cin), 351).to(BF)
+    g = mk((rows, cout), 352).to(BF)
+    dw = torch.zeros(cout, cin, 1, 1, device="cuda")
+    took_tma(lib, lambda: run_wgrad(lib, 1, 0, lazy(x, cin), lazygrad(g, cout), n, h, w, cin, cout, dw))
+    ref = (g.float().t() @ x.float()).view(cout, cin, 1, 1)
+    assert rel_err(dw, ref) < DW_TOL
+
+
+@pytest.mark.parametrize("cin,cout,n,h,w", [(2048, 512, 4, 16, 16), (512, 256, 2, 32, 32), (256, 128, 2, 64, 64),
+                                            (64, 32, 1, 8, 16)])
+def test_tma_wgradT(lib, cin, cout, n, h, w):
+    rows = n * h * w
+    x = mk((rows, cin), 361).to(BF)
+    g = mk((rows * 4, cout), 362).to(BF)
+    dw = torch.zeros(cin, cout, 2, 2, device="cuda")
+    db = torch.zeros(cout, device="cuda")
+    took_tma(lib, lambda: run_wgrad(lib, 1, 2, lazy(x, cin), lazygrad(g, cout), n, h, w, cin, cout, dw, db))
+    g6 = nchw(g, n, 2 * h, 2 * w).view(n, cout, h, 2, w, 2)
+    ref = torch.einsum("nihw,nohywx->ioyx", nchw(x, n, h, w), g6)
+    assert rel_err(dw, ref) < DW_TOL
+    assert rel_err(db, nchw(g, n, 2 * h, 2 * w).sum((0, 2, 3))) < DW_TOL
