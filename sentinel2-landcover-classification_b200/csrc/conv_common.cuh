@@ -1,6 +1,8 @@
 // conv_common.cuh — operand loaders and the epilogue of the implicit-GEMM convolution family,
 // shared by the CUDA-core engine (igemm_simt.cu) and the tcgen05 engine (igemm_tc.cu).
 #pragma once
+#include <cuda.h>   // CUtensorMap (types only: no link-time dependency on libcuda)
+
 #include "common.cuh"
 
 namespace s2lc {
@@ -166,6 +168,11 @@ __device__ __forceinline__ int64_t wgrad_index(const WgradArgs& P, int n, int k)
   return ((int64_t)k * P.Cout + co) * 4 + q;
 }
 
+// shared TMA helpers (twgrad_tc.cu): bf16 tensor map, SWIZZLE_128B, zero fill outside the tensor (dims / box fastest
+// dimension first, strides in ELEMENTS for dimensions 1..rank-1); per-channel sum of a bf16 [rows, C] tensor -> fp32
+bool make_tma_map_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_el,
+                       const uint32_t* box);
+void launch_colsum_bf16(const void* g, int64_t ld, int64_t rows, int C, float* dbias, cudaStream_t st);
 void note_simt_fallback();
 void note_tma_launch();
 int32_t launch_conv_simt(const ConvArgs& A, cudaStream_t st);

@@ -286,6 +286,18 @@ static bool tg_make_map(CUtensorMap* map, const void* base, int rank, const uint
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+bool make_tma_map_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_el,
+                       const uint32_t* box) {
+  return tg_make_map(map, base, rank, dims, strides_el, box);
+}
+void launch_colsum_bf16(const void* g, int64_t ld, int64_t rows, int C, float* dbias, cudaStream_t st) {
+  const int cv = C / 8;
+  const int cvb = cv < 256 ? cv : 256, rows_par = 256 / cvb;
+  int64_t blocks = (rows + (int64_t)rows_par * 16 - 1) / ((int64_t)rows_par * 16);
+  if (blocks > 4 * kNumSMs) blocks = 4 * kNumSMs;
+  if (blocks < 1) blocks = 1;
+  tg_colsum_kernel<<<(int)blocks, 256, cvb * 8 * sizeof(float), st>>>(reinterpret_cast<const bf16*>(g), ld, rows, C, dbias);
+}
 static bool tg_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // Returns 0 if launched, <0 on error, 1 if this shape / operand is left to the loader-warp engines.
@@ -394,16 +406,7 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
     }
     attr_set = true;
   }
-  if (A.dbias) {
-    const int64_t grows = M * (K.kind == 2 ? 4 : 1);
-    const int cv = A.Cout / 8;
-    const int cvb = cv < 256 ? cv : 256, rows_par = 256 / cvb;
-    int64_t blocks = (grows + (int64_t)rows_par * 16 - 1) / ((int64_t)rows_par * 16);
-    if (blocks > 2 * sms) blocks = 2 * sms;
-    if (blocks < 1) blocks = 1;
-    tg_colsum_kernel<<<(int)blocks, 256, cvb * 8 * sizeof(float), st>>>(reinterpret_cast<const bf16*>(A.g.dy),
-                                                                        A.g.ld_dy, grows, A.Cout, A.dbias);
-  }
+  if (A.dbias) launch_colsum_bf16(A.g.dy, A.g.ld_dy, M * (K.kind == 2 ? 4 : 1), A.Cout, A.dbias, st);
   const int grid = sms < K.items ? sms : K.items;
   twgrad_kernel<<<grid, TG_THREADS, smem, st>>>(A, K, tmA, tmG);
   note_tma_launch();
