@@ -21,7 +21,9 @@
 namespace s2lc {
 namespace dw2 {
 
-constexpr int CB = 64;   // channels per CTA block (lane = channel pair)
+// Channels per CTA block are a template parameter CB in {64, 32}.  CB = 64: lane = channel pair, a warp row is one
+// pixel.  CB = 32: 16 lanes per pixel and the two half-warps own different pixels of the strip (strip = 16R wide), so
+// layers with 24 / 144 channels fill 75 % / 90 % of the lanes instead of 37 % / 75 %.
 constexpr int NT = 256;  // threads per CTA
 
 __device__ __forceinline__ void ffma2(float2& d, const float2& a, const float2& b) {
@@ -148,14 +150,16 @@ __device__ __forceinline__ float2 ffma2r(const float2& a, const float2& b, const
 //  * WIDE (WW >= 32): thread (px = tid/8, v8 = tid%8) owns the same pixel column in every row (slot j = row j, no
 //    divisions, one bounds check per item) and the WW-32 halo columns go to ONE extra slot of the low threads;
 //  * narrow windows: generic q = tid + j*256 -> (row, px) by constant division.
-template <typename T, int NSRC, int WW, int NEW, int NRING, bool FAST>
+template <typename T, int NSRC, int WW, int NEW, int NRING, bool FAST, int CB>
 struct Loader {
-  static constexpr bool WIDE = WW >= 32;
-  static constexpr int XC = WIDE ? WW - 32 : 0;              // halo columns beyond the 32 main ones
-  static constexpr int NX = NEW * XC * 8;                    // their vectors per pass
+  static constexpr int CBV = CB / 8;                         // 8-channel vectors per pixel
+  static constexpr int MC = NT / CBV;                        // main pixel columns: one per CBV threads
+  static constexpr bool WIDE = WW >= MC;
+  static constexpr int XC = WIDE ? WW - MC : 0;              // halo columns beyond the main ones
+  static constexpr int NX = NEW * XC * CBV;                  // their vectors per pass
   static constexpr int NXT = NX > 0 ? 1 : 0;
   static_assert(NX <= NT, "halo columns of a pass must fit one slot");
-  static constexpr int NVT = WIDE ? NEW + NXT : (NEW * WW * 8 + NT - 1) / NT;
+  static constexpr int NVT = WIDE ? NEW + NXT : (NEW * WW * CBV + NT - 1) / NT;
   static constexpr int VB = 8 * sizeof(T);                   // bytes per 8-channel vector
   static constexpr int STAGE_BYTES = NVT * NSRC * NT * VB;
 
@@ -174,9 +178,9 @@ struct Loader {
   __device__ __forceinline__ void begin_item(const T* s0, int64_t ld0, const T* s1, int64_t ld1, int n_, int Hs_,
                                              int Ws_, int gy0_, int gx0_, int cb0_, int C_) {
     gy0 = gy0_; Hs = Hs_;
-    const int c8 = cb0_ + (threadIdx.x & 7) * 8;
+    const int c8 = cb0_ + (threadIdx.x % CBV) * 8;
     if (WIDE) {
-      const int px = threadIdx.x >> 3;
+      const int px = threadIdx.x / CBV;
       const int gx = gx0_ + px;
       okm = gx >= 0 && gx < Ws_ && c8 < C_;
       const int64_t img = (int64_t)n_ * Hs_ * Ws_;
@@ -185,8 +189,8 @@ struct Loader {
       rstride[0] = (int64_t)Ws_ * ld0;
       rstride[1] = (int64_t)Ws_ * ld1;
       if (NXT) {
-        erow = threadIdx.x / (XC * 8 > 0 ? XC * 8 : 1);
-        epx = 32 + ((threadIdx.x - erow * (XC * 8)) >> 3);
+        erow = threadIdx.x / (XC * CBV > 0 ? XC * CBV : 1);
+        epx = MC + ((threadIdx.x - erow * (XC * CBV)) / CBV);
         const int gxe = gx0_ + epx;
         oke = (int)threadIdx.x < NX && gxe >= 0 && gxe < Ws_ && c8 < C_;
         pe[0] = s0 + (img + gxe) * ld0 + c8;
@@ -222,12 +226,12 @@ struct Loader {
         if (oke && erow < nrows && gy >= 0 && gy < Hs) fetch(stage, NEW, pe[0] + gy * rstride[0], pe[1] + gy * rstride[1]);
       }
     } else {
-      const int c8 = cb0 + (threadIdx.x & 7) * 8;
+      const int c8 = cb0 + (threadIdx.x % CBV) * 8;
 #pragma unroll
       for (int j = 0; j < NVT; ++j) {
         int q = threadIdx.x + j * NT;
-        int row = q / (WW * 8);
-        int px = (q - row * (WW * 8)) >> 3;
+        int row = q / (WW * CBV);
+        int px = (q - row * (WW * CBV)) / CBV;
         int gy = gy0 + rel0 + row, gx = gx0 + px;
         if (row < nrows && gy >= 0 && gy < Hs && gx >= 0 && gx < Ws && c8 < C) {
           int64_t r = ((int64_t)n * Hs + gy) * Ws + gx;
@@ -243,7 +247,7 @@ struct Loader {
   // mode 1: v = (aux0*rs) * v + aux1 * z + aux2;  mode 2: v = v * rs
   static __device__ __forceinline__ void xform_store(const unsigned char* stage, int j, bool ok, float* dst,
                                                      const float* aux, int mode, int act, float rs) {
-    const int v8 = threadIdx.x & 7;
+    const int v8 = threadIdx.x % CBV;
     float v[8];
     if (ok) {
       Raw8<T>::unpack(slot(const_cast<unsigned char*>(stage), j, 0), v);
@@ -295,7 +299,7 @@ struct Loader {
   __device__ __forceinline__ void commit(const unsigned char* stage, float* tile, const float* aux, int rel0, int rbase,
                                          int nrows, int mode, int act, float rs) const {
     if (WIDE) {
-      const int px = threadIdx.x >> 3;
+      const int px = threadIdx.x / CBV;
 #pragma unroll
       for (int j = 0; j < NEW; ++j) {
         if (j >= nrows) break;
@@ -313,12 +317,12 @@ struct Loader {
         }
       }
     } else {
-      const int c8 = cb0 + (threadIdx.x & 7) * 8;
+      const int c8 = cb0 + (threadIdx.x % CBV) * 8;
 #pragma unroll
       for (int j = 0; j < NVT; ++j) {
         int q = threadIdx.x + j * NT;
-        int row = q / (WW * 8);
-        int px = (q - row * (WW * 8)) >> 3;
+        int row = q / (WW * CBV);
+        int px = (q - row * (WW * CBV)) / CBV;
         if (row >= nrows) continue;
         int gy = gy0 + rel0 + row, gx = gx0 + px;
         bool ok = gy >= 0 && gy < Hs && gx >= 0 && gx < Ws && c8 < C;
@@ -338,9 +342,10 @@ struct Geom {
   int xs, ychunks, YC;
 };
 
+template <int CB>
 __device__ __forceinline__ void flush_stats(float2 s0, float2 s1, float* sstat, int cb0, int C, double* stats) {
   // sstat: [2][CB] floats, zeroed at kernel start
-  const int lane = threadIdx.x & 31;
+  const int lane = (threadIdx.x & 31) % (CB / 2);
   atomicAdd(&sstat[2 * lane], s0.x);
   atomicAdd(&sstat[2 * lane + 1], s0.y);
   atomicAdd(&sstat[CB + 2 * lane], s1.x);
@@ -355,9 +360,10 @@ __device__ __forceinline__ void flush_stats(float2 s0, float2 s1, float* sstat, 
 // ---------------------------------------------------------------------------------------------------------
 // Forward: out[o] = sum_k w[k] * act(bn(in))[o*S + k - pad]; epilogue: raw output + BatchNorm moments.
 // R = pixels per warp (strip = 8R wide), RY = rows per step, D = cp.async passes in flight.
-template <typename T, int K, int S, int R, int RY, int D>
+template <typename T, int K, int S, int R, int RY, int D, int CB>
 struct FwdCfg {
-  static constexpr int TW = 8 * R;                 // destination pixels per strip (8 warps x R)
+  static constexpr int NH = 64 / CB;               // pixel groups per warp (half-warps own different pixels)
+  static constexpr int TW = 8 * R * NH;            // destination pixels per strip (8 warps x NH x R)
   static constexpr int WW = (TW - 1) * S + K;      // staged window width
   static constexpr int WIN = (RY - 1) * S + K;     // staged window height per step
   static constexpr int NEW = RY * S;               // new source rows per step
@@ -366,15 +372,15 @@ struct FwdCfg {
   static constexpr int PRO = WIN - NEW;            // rows staged before the first step
   static constexpr int PRO_PASSES = (PRO + NEW - 1) / NEW;
   static constexpr int NSTAGE = D + PRO_PASSES;
-  using Ld = Loader<T, 1, WW, NEW, NRING, sizeof(T) == 2>;
+  using Ld = Loader<T, 1, WW, NEW, NRING, sizeof(T) == 2, CB>;
   static constexpr size_t RING_BYTES = sizeof(float) * (size_t)NRING * WW * CB;
   static constexpr size_t SMEM = RING_BYTES + sizeof(float) * 4 * CB + (size_t)NSTAGE * Ld::STAGE_BYTES;
 };
 
-template <typename T, int K, int S, int R, int RY, int D, int MINB>
+template <typename T, int K, int S, int R, int RY, int D, int MINB, int CB>
 __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const float* __restrict__ w,
                                                            T* __restrict__ out, double* stats, Geom g) {
-  using Cfg = FwdCfg<T, K, S, R, RY, D>;
+  using Cfg = FwdCfg<T, K, S, R, RY, D, CB>;
   using Ld = typename Cfg::Ld;
   constexpr int WW = Cfg::WW, WIN = Cfg::WIN, NEW = Cfg::NEW, NRING = Cfg::NRING, VW = Cfg::VW, PRO = Cfg::PRO,
                 PRO_PASSES = Cfg::PRO_PASSES, NSTAGE = Cfg::NSTAGE;
@@ -383,7 +389,8 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
   float* aux = tile + (size_t)NRING * WW * CB;  // [2][CB] scale, shift
   float* sstat = aux + 2 * CB;                   // [2][CB]
   unsigned char* stages = reinterpret_cast<unsigned char*>(sstat + 2 * CB);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int HL = CB / 2, NH = Cfg::NH;              // lanes per pixel group, pixel groups per warp
+  const int lane = (threadIdx.x & 31) % HL, pg = (threadIdx.x >> 5) * NH + (threadIdx.x & 31) / HL;
   const int cb0 = blockIdx.y * CB;
   const int c = cb0 + 2 * lane;
   const bool cvalid = c < g.C;
@@ -441,7 +448,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
       for (int dy = 0; dy < RY; ++dy)
 #pragma unroll
         for (int r = 0; r < R; ++r) acc[dy][r] = make_float2(0.f, 0.f);
-      const float* tl = tile + (warp * R * S) * CB + 2 * lane;
+      const float* tl = tile + (pg * R * S) * CB + 2 * lane;
 #pragma unroll
       for (int j = 0; j < WIN; ++j) {
         int slot = base + j;
@@ -461,7 +468,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
         }
       }
       if (cvalid) {
-        const int ox0 = x0 + warp * R;
+        const int ox0 = x0 + pg * R;
         const float2 one2 = make_float2(1.f, 1.f);
 #pragma unroll
         for (int dy = 0; dy < RY; ++dy) {
@@ -491,7 +498,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
   }
   if (stats) {
     __syncthreads();
-    flush_stats(s0, s1, sstat, cb0, g.C, stats);
+    flush_stats<CB>(s0, s1, sstat, cb0, g.C, stats);
   }
 }
 
@@ -500,11 +507,12 @@ __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const f
 // at output resolution):  dx[i] = act'(u[i]) * sum_k w[k] g[(i+PAD-k)/S]  (+ residual),
 //                         dW[k] += act(u[i]) * g[(i+PAD-k)/S],   taps with (i+PAD-k) % S == 0 only.
 // PAD is the forward top/left padding: (K-1)/2 for S=1, (K-2)/2 for S=2 with even H, W (host-checked).
-template <typename T, int K, int S, int R, int RY, int D>
+template <typename T, int K, int S, int R, int RY, int D, int CB>
 struct BwdCfg {
   static constexpr int PAD = S == 1 ? (K - 1) / 2 : (K - 2) / 2;
   static constexpr int FL = floordiv(PAD - K + 1, S);          // first source offset (in source pixels)
-  static constexpr int TW = 8 * R;
+  static constexpr int NH = 64 / CB;
+  static constexpr int TW = 8 * R * NH;
   static constexpr int WW = (TW - 1 + PAD) / S - FL + 1;
   static constexpr int WIN = (RY - 1 + PAD) / S - FL + 1;
   static constexpr int NEW = RY / S;
@@ -513,19 +521,19 @@ struct BwdCfg {
   static constexpr int PRO = WIN - NEW;
   static constexpr int PRO_PASSES = (PRO + NEW - 1) / NEW;
   static constexpr int NSTAGE = D + PRO_PASSES;
-  using Ld = Loader<T, 2, WW, NEW, NRING, sizeof(T) == 2>;
+  using Ld = Loader<T, 2, WW, NEW, NRING, sizeof(T) == 2, CB>;
   static constexpr size_t RING_BYTES = sizeof(float) * (size_t)NRING * WW * CB;
   static constexpr size_t SMEM =
       RING_BYTES + sizeof(float) * (7 * CB + K * K * CB) + (size_t)NSTAGE * Ld::STAGE_BYTES;
 };
 
-template <typename T, int K, int S, int R, int RY, int D, int MINB>
+template <typename T, int K, int S, int R, int RY, int D, int MINB, int CB>
 __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, const float* __restrict__ w,
                                                            s2lc_lazy in, int apply_act_bwd,
                                                            const T* __restrict__ res, int64_t ld_res,
                                                            T* __restrict__ out, int64_t ld_out, double* stats,
                                                            float* __restrict__ dw, Geom g) {
-  using Cfg = BwdCfg<T, K, S, R, RY, D>;
+  using Cfg = BwdCfg<T, K, S, R, RY, D, CB>;
   using Ld = typename Cfg::Ld;
   constexpr bool FAST = sizeof(T) == 2;
   constexpr int WW = Cfg::WW, WIN = Cfg::WIN, NEW = Cfg::NEW, NRING = Cfg::NRING, VW = Cfg::VW, PAD = Cfg::PAD,
@@ -538,7 +546,8 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
   float* sstat = iaux + 2 * CB;                  // [2][CB]
   float* sdw = sstat + 2 * CB;                   // [K*K][CB]
   unsigned char* stages = reinterpret_cast<unsigned char*>(sdw + K * K * CB);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int HL = CB / 2, NH = Cfg::NH;
+  const int lane = (threadIdx.x & 31) % HL, pg = (threadIdx.x >> 5) * NH + (threadIdx.x & 31) / HL;
   const int cb0 = blockIdx.y * CB;
   const int c = cb0 + 2 * lane;
   const bool cvalid = c < g.C;
@@ -594,7 +603,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
         int iy = y0 + t * RY + dy;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          int ix = x0 + warp * R + r;
+          int ix = x0 + pg * R + r;
           z[dy][r].zero();
           if (cvalid && iy < yend && ix < g.Wd) z[dy][r].load(zin + (((int64_t)n * g.Hd + iy) * g.Wd + ix) * in.ld + c);
         }
@@ -630,7 +639,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
         int iy = y0 + t * RY + dy;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          int ix = x0 + warp * R + r;
+          int ix = x0 + pg * R + r;
           float2 z = zr[dy][r].get();
           bool v = cvalid && iy < yend && ix < g.Wd;
           float2 u = ffma2r(z, isc, ish);
@@ -639,7 +648,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
           acc[dy][r] = make_float2(0.f, 0.f);
         }
       }
-      const float* tl = tile + ((warp * R) / S) * CB + 2 * lane;
+      const float* tl = tile + ((pg * R) / S) * CB + 2 * lane;
 #pragma unroll
       for (int j = 0; j < WIN; ++j) {
         int slot = base + j;
@@ -664,7 +673,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
         }
       }
       if (cvalid) {
-        const int ix0 = x0 + warp * R;
+        const int ix0 = x0 + pg * R;
         const float2 one2 = make_float2(1.f, 1.f);
         const bool silu_fast = FAST && in.act == S2LC_ACT_SILU;
 #pragma unroll
@@ -725,7 +734,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
       atomicAdd(&sdw[t * CB + 2 * lane + 1], wacc[t].y);
     }
   }
-  if (stats) flush_stats(s0, s1, sstat, cb0, g.C, stats);  // contains a __syncthreads
+  if (stats) flush_stats<CB>(s0, s1, sstat, cb0, g.C, stats);  // contains a __syncthreads
   else __syncthreads();
   if (dw) {
     for (int i = threadIdx.x; i < K * K * CB; i += NT) {
@@ -769,11 +778,11 @@ static int resident_ctas(Kern kern, size_t smem) {
   return per_sm * kNumSMs;
 }
 
-template <typename T, int K, int S, int R, int RY, int D, int MINB>
+template <typename T, int K, int S, int R, int RY, int D, int MINB, int CB>
 static int32_t launch_fwd(const s2lc_lazy* in, const float* w, void* out, double* stats, int N, int H, int W, int C,
                           cudaStream_t st) {
-  using Cfg = FwdCfg<T, K, S, R, RY, D>;
-  auto kern = dw2_fwd_kernel<T, K, S, R, RY, D, MINB>;
+  using Cfg = FwdCfg<T, K, S, R, RY, D, CB>;
+  auto kern = dw2_fwd_kernel<T, K, S, R, RY, D, MINB, CB>;
   int32_t r = set_smem(kern, Cfg::SMEM);
   if (r) return r;
   Geom g{};
@@ -793,12 +802,12 @@ static int32_t launch_fwd(const s2lc_lazy* in, const float* w, void* out, double
   return check_launch("dwconv2_fwd");
 }
 
-template <typename T, int K, int S, int R, int RY, int D, int MINB>
+template <typename T, int K, int S, int R, int RY, int D, int MINB, int CB>
 static int32_t launch_bwd(const s2lc_lazygrad* gin, const float* w, const s2lc_lazy* in, int apply_act_bwd,
                           const void* res, int64_t ld_res, void* out, int64_t ld_out, double* stats, float* dw, int N,
                           int H, int W, int C, cudaStream_t st) {
-  using Cfg = BwdCfg<T, K, S, R, RY, D>;
-  auto kern = dw2_bwd_kernel<T, K, S, R, RY, D, MINB>;
+  using Cfg = BwdCfg<T, K, S, R, RY, D, CB>;
+  auto kern = dw2_bwd_kernel<T, K, S, R, RY, D, MINB, CB>;
   int32_t r = set_smem(kern, Cfg::SMEM);
   if (r) return r;
   Geom g{};
@@ -824,23 +833,28 @@ using namespace s2lc;
 
 // geometry choice per (K, S, width): R = pixels per warp (strip = 8R pixels wide), RY = rows per step, D = cp.async
 // passes in flight; sized so that two CTAs fit an SM (shared memory <= 113 KB) wherever registers allow it.
-#define DW2_F(T, K_, S_, R_, RY_, D_, MB) \
-  return dw2::launch_fwd<T, K_, S_, R_, RY_, D_, MB>(in, w, out, stats, N, H, W, C, st)
+#define DW2_F(T, K_, S_, R_, RY_, D_, MB, CB_) \
+  return dw2::launch_fwd<T, K_, S_, R_, RY_, D_, MB, CB_>(in, w, out, stats, N, H, W, C, st)
+// `half`: the last 64-channel block would be at most half full (C = 24, 144, ...) and rows are >= 64 px wide: 32-channel
+// blocks with two pixel groups per warp
 #define DW2_FWD_BF16                                     \
   if (s == 1) {                                          \
-    if (wide) { if (k == 3) DW2_F(s2lc::bf16, 3, 1, 4, 4, 2, 2); DW2_F(s2lc::bf16, 5, 1, 4, 2, 2, 2); } \
-    if (k == 3) DW2_F(s2lc::bf16, 3, 1, 2, 4, 3, 2);     \
-    DW2_F(s2lc::bf16, 5, 1, 2, 4, 3, 2);                 \
+    if (wide) {                                          \
+      if (k == 3) { if (half) DW2_F(s2lc::bf16, 3, 1, 4, 4, 2, 2, 32); DW2_F(s2lc::bf16, 3, 1, 4, 4, 2, 2, 64); } \
+      DW2_F(s2lc::bf16, 5, 1, 4, 2, 2, 2, 64);           \
+    }                                                    \
+    if (k == 3) DW2_F(s2lc::bf16, 3, 1, 2, 4, 3, 2, 64); \
+    DW2_F(s2lc::bf16, 5, 1, 2, 4, 3, 2, 64);             \
   }                                                      \
-  if (k == 3) DW2_F(s2lc::bf16, 3, 2, 2, 2, 2, 2);       \
-  DW2_F(s2lc::bf16, 5, 2, 2, 1, 3, 2);
+  if (k == 3) { if (half) DW2_F(s2lc::bf16, 3, 2, 2, 2, 2, 2, 32); DW2_F(s2lc::bf16, 3, 2, 2, 2, 2, 2, 64); } \
+  DW2_F(s2lc::bf16, 5, 2, 2, 1, 3, 2, 64);
 #define DW2_FWD_F32                                      \
   if (s == 1) {                                          \
-    if (k == 3) DW2_F(float, 3, 1, 2, 4, 1, 1);          \
-    DW2_F(float, 5, 1, 2, 4, 1, 1);                      \
+    if (k == 3) DW2_F(float, 3, 1, 2, 4, 1, 1, 64);      \
+    DW2_F(float, 5, 1, 2, 4, 1, 1, 64);                  \
   }                                                      \
-  if (k == 3) DW2_F(float, 3, 2, 2, 2, 1, 1);            \
-  DW2_F(float, 5, 2, 2, 1, 1, 1);
+  if (k == 3) DW2_F(float, 3, 2, 2, 2, 1, 1, 64);        \
+  DW2_F(float, 5, 2, 2, 1, 1, 1, 64);
 
 extern "C" {
 
@@ -851,6 +865,7 @@ int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* 
   S2LC_REQUIRE(in->gate == nullptr, S2LC_ERR_SHAPE, "dwconv: gated input is not a reference configuration");
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = W > 16;
+  const bool half = W >= 64 && ((C + 63) % 64) < 32;     // channels in the last 64-block: ((C - 1) % 64) + 1 <= 32
   if (dtype == S2LC_BF16) { DW2_FWD_BF16 }
   if (dtype == S2LC_F32) { DW2_FWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);
@@ -858,25 +873,31 @@ int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* 
 }
 
 
-#define DW2_B(T, K_, S_, R_, RY_, D_, MB)                                                                         \
-  return dw2::launch_bwd<T, K_, S_, R_, RY_, D_, MB>(g, w, in, apply_act_bwd, res, ld_res, out, ld_out, stats, dw, N, \
-                                                     H, W, C, st)
+#define DW2_B(T, K_, S_, R_, RY_, D_, MB, CB_)                                                                          \
+  return dw2::launch_bwd<T, K_, S_, R_, RY_, D_, MB, CB_>(g, w, in, apply_act_bwd, res, ld_res, out, ld_out, stats, dw, \
+                                                          N, H, W, C, st)
 #define DW2_BWD_BF16                                     \
   if (s == 1) {                                          \
-    if (wide) { if (k == 3) DW2_B(s2lc::bf16, 3, 1, 4, 2, 2, 2); DW2_B(s2lc::bf16, 5, 1, 4, 2, 4, 1); } \
-    if (k == 3) DW2_B(s2lc::bf16, 3, 1, 2, 4, 2, 2);     \
-    DW2_B(s2lc::bf16, 5, 1, 2, 2, 4, 1);                 \
+    if (wide) {                                          \
+      if (k == 3) { if (half) DW2_B(s2lc::bf16, 3, 1, 4, 2, 2, 2, 32); DW2_B(s2lc::bf16, 3, 1, 4, 2, 2, 2, 64); } \
+      DW2_B(s2lc::bf16, 5, 1, 4, 2, 4, 1, 64);           \
+    }                                                    \
+    if (k == 3) DW2_B(s2lc::bf16, 3, 1, 2, 4, 2, 2, 64); \
+    DW2_B(s2lc::bf16, 5, 1, 2, 2, 4, 1, 64);             \
   }                                                      \
-  if (wide) { if (k == 3) DW2_B(s2lc::bf16, 3, 2, 4, 4, 2, 2); DW2_B(s2lc::bf16, 5, 2, 4, 2, 4, 1); } \
-  if (k == 3) DW2_B(s2lc::bf16, 3, 2, 2, 4, 2, 2);       \
-  DW2_B(s2lc::bf16, 5, 2, 2, 2, 4, 1);
+  if (wide) {                                            \
+    if (k == 3) { if (half) DW2_B(s2lc::bf16, 3, 2, 4, 4, 2, 2, 32); DW2_B(s2lc::bf16, 3, 2, 4, 4, 2, 2, 64); } \
+    DW2_B(s2lc::bf16, 5, 2, 4, 2, 4, 1, 64);             \
+  }                                                      \
+  if (k == 3) DW2_B(s2lc::bf16, 3, 2, 2, 4, 2, 2, 64);   \
+  DW2_B(s2lc::bf16, 5, 2, 2, 2, 4, 1, 64);
 #define DW2_BWD_F32                                      \
   if (s == 1) {                                          \
-    if (k == 3) DW2_B(float, 3, 1, 2, 2, 1, 1);          \
-    DW2_B(float, 5, 1, 2, 2, 1, 1);                      \
+    if (k == 3) DW2_B(float, 3, 1, 2, 2, 1, 1, 64);      \
+    DW2_B(float, 5, 1, 2, 2, 1, 1, 64);                  \
   }                                                      \
-  if (k == 3) DW2_B(float, 3, 2, 2, 2, 1, 1);            \
-  DW2_B(float, 5, 2, 2, 2, 1, 1);
+  if (k == 3) DW2_B(float, 3, 2, 2, 2, 1, 1, 64);        \
+  DW2_B(float, 5, 2, 2, 2, 1, 1, 64);
 
 /* Fused depthwise backward: dx (data gradient w.r.t. the BatchNorm output feeding the conv, times act' when
  * apply_act_bwd) + BNBWD statistics of dx against in.raw + dW, in one pass. */
@@ -896,6 +917,7 @@ int32_t s2lc_dwconv_bwd(const s2lc_lazygrad* g, const float* w, const s2lc_lazy*
   }
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = W > 16;
+  const bool half = W >= 64 && ((C + 63) % 64) < 32;
   if (dtype == S2LC_BF16) { DW2_BWD_BF16 }
   if (dtype == S2LC_F32) { DW2_BWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);

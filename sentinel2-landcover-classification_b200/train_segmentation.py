@@ -161,6 +161,7 @@ class DataParallelTrainer(SegmentationStep):
             dist.broadcast(self.optimizer.flat_param, src=0, group=self.pg)
 
     snapshot: torch.Tensor | None = None   # bench.py dp_check: receives every bucket's LOCAL values at fire time
+    snapshot_only: bool = False            # ... and skips the all-reduce (the pass then ends with the local gradient)
 
     def _bucket_ready(self, bucket_index: int) -> None:
         ev = torch.cuda.Event()
@@ -170,7 +171,8 @@ class DataParallelTrainer(SegmentationStep):
             if self.snapshot is not None:
                 a, b = self.buckets[bucket_index][:2]
                 self.snapshot[a:b].copy_(self.eng.flat_grad[a:b])
-            self.reducer.reduce(bucket_index)
+            if not self.snapshot_only:
+                self.reducer.reduce(bucket_index)
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         loss = self.forward_backward(x, y)

@@ -63,7 +63,9 @@ def lazygrad(dy, ld, z=None, p=None, q=None, t=None, rs=None):
 # ----------------------------------------------------------------------------------------------- dwconv
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])
 @pytest.mark.parametrize("k,s,h,w,c", [(3, 1, 24, 40, 48), (5, 1, 16, 16, 72), (3, 2, 32, 32, 144), (5, 2, 28, 28, 64),
-                                       (5, 2, 7, 7, 24), (3, 2, 15, 17, 8)])
+                                       (5, 2, 7, 7, 24), (3, 2, 15, 17, 8),
+                                       # rows >= 64 px with a last channel block <= half full: 32-channel blocks
+                                       (3, 1, 20, 72, 24), (3, 2, 24, 136, 144), (3, 1, 10, 64, 32), (3, 2, 20, 64, 88)])
 def test_dwconv_fwd_bwd(lib, prec, k, s, h, w, c):
     dtype, dt, tol = DT[prec]
     n = 2
