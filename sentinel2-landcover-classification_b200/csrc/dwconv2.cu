@@ -865,7 +865,8 @@ int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* 
   S2LC_REQUIRE(in->gate == nullptr, S2LC_ERR_SHAPE, "dwconv: gated input is not a reference configuration");
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = W > 16;
-  const bool half = W >= 64 && ((C + 63) % 64) < 32;     // channels in the last 64-block: ((C - 1) % 64) + 1 <= 32
+  // 32-channel blocks: last 64-block at most half full, or rows >= 128 px (two pixel groups per warp are 5-10 % faster there)
+  const bool half = W >= 64 && (((C + 63) % 64) < 32 || W >= 128 || (s2lc::debug_flags() & s2lc::DBG_DW_CB32));
   if (dtype == S2LC_BF16) { DW2_FWD_BF16 }
   if (dtype == S2LC_F32) { DW2_FWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);
@@ -917,7 +918,7 @@ int32_t s2lc_dwconv_bwd(const s2lc_lazygrad* g, const float* w, const s2lc_lazy*
   }
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = W > 16;
-  const bool half = W >= 64 && ((C + 63) % 64) < 32;
+  const bool half = W >= 64 && (((C + 63) % 64) < 32 || W >= 128 || (s2lc::debug_flags() & s2lc::DBG_DW_CB32));
   if (dtype == S2LC_BF16) { DW2_BWD_BF16 }
   if (dtype == S2LC_F32) { DW2_BWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);

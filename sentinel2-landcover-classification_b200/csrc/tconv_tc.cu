@@ -19,6 +19,7 @@
 // Two TMEM accumulators: the epilogue of tile i overlaps the main loop of tile i+1.
 #include <cuda.h>
 
+#include <cstring>
 #include <type_traits>
 
 #include "conv_common.cuh"
@@ -44,6 +45,8 @@ struct TPlan {
   int tiles_x, tiles_y;
   int stages, stage_bytes;
   int tmem_cols;
+  int epi_tma;       // 1: epilogue through a shared-memory staging tile, TMA bulk stores and a column pass for the moments
+  int stage_out;     // bytes of the staging tile (ceil(BN / 64) boxes of 128 rows x 128 B)
 };
 
 // ---- TMA / mbarrier transaction wrappers ---------------------------------------------------------------------
@@ -90,15 +93,29 @@ __device__ __forceinline__ TTile tile_of(const ConvArgs& P, const TPlan& K, int 
   return T;
 }
 
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan K, const __grid_constant__ CUtensorMap tmA,
-                                                              const __grid_constant__ CUtensorMap tmB) {
+                                                              const __grid_constant__ CUtensorMap tmB,
+                                                              const __grid_constant__ CUtensorMap tmO) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   // per-channel statistics of ALL column tiles this CTA visits, [2][n_tiles * BN] floats, flushed once at the end
   // (a flush per tile is two fp64 atomics per column from every CTA on the same addresses: on the thin layers —
   // 16 k tiles of 128 x 144 — the L2 atomic unit, not the tensor core, set the pace)
-  float* sstat = reinterpret_cast<float*>(smem + K.stages * K.stage_bytes);
+  unsigned char* ostage = smem + K.stages * K.stage_bytes;     // staging tile of the TMA-store epilogue (1024 B aligned)
+  float* sstat = reinterpret_cast<float*>(ostage + K.stage_out);
   const int NS = K.n_tiles * K.BN;
   uint64_t* full = reinterpret_cast<uint64_t*>(sstat + 2 * NS);
   uint64_t* empty = full + TV_MAX_STAGES;
@@ -206,6 +223,106 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
     };
     int b = 0;
     uint32_t bph = 0;
+    if (K.epi_tma) {
+      // ---------------------------------------------------------------- TMA-store epilogue (plain forward convs and
+      // data gradients without residual / act' operands).  Per 16-column chunk a thread only adds the bias, rounds and
+      // writes 2 x 16 B into the swizzled staging tile; one lane then stores the tile with bulk tensor copies (whole
+      // 128 B lines, rows / columns outside the tensor are clipped by the copy) and the BatchNorm moments come from a
+      // column pass over the staged bf16 values: ~5 instructions per element pair instead of two 16-lane butterflies
+      // per chunk.  The thin-K layers (expand convs, project-conv data gradients) are bound by exactly this code.
+      const int etid = ew * 32 + lane;
+      constexpr int NE = TV_EPI_WARPS * 32;
+      const uint32_t ost = smem_u32(ostage);
+      const int boxes = (K.BN + 63) >> 6;
+      const int CP = K.BN >> 1;                                   // column pairs of the tile
+      const int G = NE / CP > 0 ? NE / CP : 1;                    // row groups of the column pass
+      const uint32_t rsw = (uint32_t)(r & 7);
+      for (int t = blockIdx.x; t < K.total_tiles; t += gridDim.x) {
+        const TTile T = tile_of(P, K, t);
+        const int n0 = T.nt * K.BN;
+        int rows_valid = 128;
+        if (K.taps != 9) {
+          const int64_t left = M - T.m0;
+          rows_valid = left < 128 ? (int)left : 128;
+        }
+        mbar_wait(&acc_full[b], bph);
+        tc_fence_after();
+        // the previous tile's bulk stores must have finished READING the staging tile
+        if (etid == 0) tma_store_wait_read();
+        asm volatile("bar.sync 1, %0;" ::"n"(NE) : "memory");
+        for (int cj = sub; cj < nchunks; cj += NSUB) {
+          const int col0 = n0 + cj * 16;
+          const int nvalid = P.Nout - col0;
+          if (nvalid <= 0) break;
+          float acc[16];
+          tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * K.BN + cj * 16), acc);
+          if (P.bias) {
+            if (nvalid >= 16) {
+              const float4* bv = reinterpret_cast<const float4*>(P.bias + col0);
+#pragma unroll
+              for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 tb = __ldg(bv + j4);
+                acc[4 * j4] += tb.x; acc[4 * j4 + 1] += tb.y; acc[4 * j4 + 2] += tb.z; acc[4 * j4 + 3] += tb.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j < nvalid) acc[j] += __ldg(P.bias + col0 + j);
+            }
+          }
+          uint4 o0, o1;
+          {
+            __nv_bfloat162* h0 = reinterpret_cast<__nv_bfloat162*>(&o0);
+            __nv_bfloat162* h1 = reinterpret_cast<__nv_bfloat162*>(&o1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              h0[j] = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+              h1[j] = __floats2bfloat162_rn(acc[8 + 2 * j], acc[8 + 2 * j + 1]);
+            }
+          }
+          // tile column cj*16 .. +15 = box cj/4, 16 B chunks 2*(cj%4), +1 of row r's 128 B line (SWIZZLE_128B)
+          const uint32_t line = ost + (uint32_t)((cj >> 2) * 16384) + (uint32_t)(r >> 3) * 1024u + rsw * 128u;
+          const uint32_t ch = (uint32_t)((cj & 3) * 2);
+          sts16(line + (((ch) ^ rsw) << 4), o0);
+          sts16(line + (((ch + 1) ^ rsw) << 4), o1);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) sc_mbar_arrive(&acc_empty[b]);
+        fence_proxy_async();
+        asm volatile("bar.sync 1, %0;" ::"n"(NE) : "memory");
+        if (etid == 0) {
+          for (int j = 0; j < boxes; ++j) {
+            if (n0 + j * 64 >= P.Nout) break;
+            if (K.taps == 9) tma_store_4d(&tmO, ost + (uint32_t)(j * 16384), n0 + j * 64, T.x0, T.y0, T.n);
+            else tma_store_2d(&tmO, ost + (uint32_t)(j * 16384), n0 + j * 64, (int)T.m0);
+          }
+          tma_store_commit();
+        }
+        if (stats_kind == S2LC_STATS_MOMENTS) {
+          const int cp = etid % CP, g = etid / CP;
+          if (g < G && n0 + 2 * cp < P.Nout) {
+            // word (row rr, column pair cp): box cp/32, 16 B chunk (cp%32)/4, word cp%4
+            const uint32_t base = ost + (uint32_t)((cp >> 5) * 16384) + (uint32_t)((cp & 3) * 4);
+            const uint32_t c16 = (uint32_t)((cp & 31) >> 2);
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+            for (int rr = g; rr < rows_valid; rr += G) {
+              uint32_t w;
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w)
+                           : "r"(base + (uint32_t)(rr >> 3) * 1024u + (uint32_t)(rr & 7) * 128u + ((c16 ^ (uint32_t)(rr & 7)) << 4)));
+              const float x0 = __uint_as_float(w << 16), x1 = __uint_as_float(w & 0xffff0000u);
+              a0.x += x0; a0.y += x1;
+              a1.x = fmaf(x0, x0, a1.x); a1.y = fmaf(x1, x1, a1.y);
+            }
+            float* gs = sstat + n0 + 2 * cp;
+            atomicAdd(gs, a0.x); atomicAdd(gs + 1, a0.y);
+            atomicAdd(gs + NS, a1.x); atomicAdd(gs + NS + 1, a1.y);
+          }
+        }
+        if (++b == 2) { b = 0; bph ^= 1u; }
+      }
+      if (etid == 0) tma_store_wait_all();
+    } else
     for (int t = blockIdx.x; t < K.total_tiles; t += gridDim.x) {
       const TTile T = tile_of(P, K, t);
       const int n0 = T.nt * K.BN;
@@ -485,8 +602,13 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
   // the rolling-row engine, sconv_tc.cu); 1x1 and transposed convs from 176 / 128 input channels (below that the
   // tile is all epilogue and the 12-epilogue-warp streaming engine is as fast or faster).
   const bool take_all = (dbg & DBG_TMA_ALL) != 0;
+  // epilogue without per-row global operands -> shared-memory staging + TMA bulk stores (see the kernel)
+  const bool epi_ok = A.mode != S2LC_CONVT_FWD && !A.has_prev && !A.res1 && !A.res2 && A.Nout % 8 == 0 &&
+                      (A.stats_kind == S2LC_STATS_NONE || A.stats_kind == S2LC_STATS_MOMENTS) && !(dbg & DBG_NO_TMA_STORE);
   if (!take_all) {
-    if (A.mode == S2LC_CONV_1X1 && A.C < 176) return 1;
+    // thin-K 1x1 layers (expand convs) are all epilogue: with the TMA-store epilogue this engine writes 2.2-2.5 TB/s
+    // where the streaming engine reaches 1.1-1.5 (profiles/r02g_tma_sweep.txt); without it, or with N < 64, it loses
+    if (A.mode == S2LC_CONV_1X1 && A.C < 176 && !(epi_ok && A.Nout >= 64)) return 1;
     if (A.mode == S2LC_CONVT_FWD && A.C < 128) return 1;
   }
   if (K.taps == 9) {
@@ -509,17 +631,37 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
   // fewer, wider column tiles reuse the A tile better; but a launch that cannot fill the SMs once is cut finer
   while ((int64_t)K.m_tiles * nt < kNumSMs && (n16 + nt) / (nt + 1) >= 64) ++nt;
   K.BN = ((n16 + nt - 1) / nt + 15) / 16 * 16;
+  // TMA-store epilogue: forward convs / data gradients whose epilogue has no per-row global operand (no residual, no
+  // act'(prev)), bf16 rows of whole 16 B vectors.  With several column tiles the tile width must be a multiple of the
+  // 64-column store box (a partial last box would spill into the next tile's columns); the copy clips at Nout.
+  const int chunks_k = K.taps * K.KC;
+  if (epi_ok) {
+    // the staging tile takes shared memory from the operand pipeline: keep >= min(4, k chunks + 1) stages
+    const int need = chunks_k + 1 < 4 ? chunks_k + 1 : 4;
+    const int cand[4] = {nt > 1 ? (K.BN + 63) / 64 * 64 : K.BN, 192, 128, 64};
+    // narrower tiles only for thin-K layers (all epilogue); compute-bound layers keep their 256-wide tiles
+    for (int i = 0; i < ((nt > 1 && chunks_k <= 6) ? 4 : 1); ++i) {
+      const int bn = cand[i];
+      if (bn > 256 || (i > 0 && bn >= cand[0])) continue;
+      const int so = (bn + 63) / 64 * 16384;
+      const int nt_e = (A.Nout + bn - 1) / bn;
+      const int fixed_e = 1024 + 2 * nt_e * bn * 4 + (2 * TV_MAX_STAGES + 4) * 8 + 64;
+      const int st_e = (226 * 1024 - fixed_e - so) / (TV_A_BYTES + bn * 128);
+      if (st_e >= need && st_e >= 2) { K.epi_tma = 1; K.stage_out = so; K.BN = bn; break; }
+    }
+  }
   K.n_tiles = (A.Nout + K.BN - 1) / K.BN;
   K.total_tiles = K.m_tiles * K.n_tiles;
   K.stage_bytes = TV_A_BYTES + K.BN * 128;
   const int fixed = 1024 + 2 * K.n_tiles * K.BN * 4 + (2 * TV_MAX_STAGES + 4) * 8 + 64;
-  K.stages = (226 * 1024 - fixed) / K.stage_bytes;
+  K.stages = (226 * 1024 - fixed - K.stage_out) / K.stage_bytes;
   if (K.stages > TV_MAX_STAGES) K.stages = TV_MAX_STAGES;
   if (K.stages < 2) return 1;
   K.tmem_cols = 32;
   while (K.tmem_cols < 2 * K.BN) K.tmem_cols *= 2;
 
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmO;
+  memset(&tmO, 0, sizeof(tmO));
   bool ok;
   if (K.taps == 9) {
     const uint64_t dims[4] = {(uint64_t)A.C, (uint64_t)A.W, (uint64_t)A.H, (uint64_t)A.N};
@@ -538,8 +680,21 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
     const uint32_t box[2] = {64, (uint32_t)K.BN};
     ok = ok && tv_make_map(&tmB, A.w_packed, 2, dims, str, box);
   }
+  if (ok && K.epi_tma) {
+    if (K.taps == 9) {
+      const uint64_t dims[4] = {(uint64_t)A.Nout, (uint64_t)A.W, (uint64_t)A.H, (uint64_t)A.N};
+      const uint64_t str[3] = {(uint64_t)A.ld_out, (uint64_t)A.W * A.ld_out, (uint64_t)A.H * A.W * A.ld_out};
+      const uint32_t box[4] = {64, (uint32_t)K.bw, (uint32_t)K.bh, 1};
+      ok = tv_make_map(&tmO, A.out, 4, dims, str, box);
+    } else {
+      const uint64_t dims[2] = {(uint64_t)A.Nout, (uint64_t)M};
+      const uint64_t str[1] = {(uint64_t)A.ld_out};
+      const uint32_t box[2] = {64, 128};
+      ok = tv_make_map(&tmO, A.out, 2, dims, str, box);
+    }
+  }
   if (!ok) return 1;   // no driver entry point / encoding refused: the other engines take the shape
-  const size_t smem = (size_t)fixed + (size_t)K.stages * K.stage_bytes;
+  const size_t smem = (size_t)fixed + (size_t)K.stage_out + (size_t)K.stages * K.stage_bytes;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(tconv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -550,7 +705,7 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
     attr_set = true;
   }
   int grid = kNumSMs < K.total_tiles ? kNumSMs : K.total_tiles;
-  tconv_kernel<<<grid, TV_THREADS, smem, st>>>(A, K, tmA, tmB);
+  tconv_kernel<<<grid, TV_THREADS, smem, st>>>(A, K, tmA, tmB, tmO);
   note_tma_launch();
   return check_launch("tconv_tc");
 }
