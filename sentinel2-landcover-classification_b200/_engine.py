@@ -518,7 +518,7 @@ class Workspace:
             lv.cat = self.act(lv.rows, lv.c_buf)
             lv.wup = pack_ct(lv.kup, up.weight)
             lv.in_op = dec_in
-            if tma and dec_in_c >= 128:
+            if tma and dec_in_c >= 64:
                 lv.in_op = self.materialize_act(dec_in, N * dec_h * dec_w, dec_in_c, dec_h * dec_w,
                                                 f"{N}x{dec_h}x{dec_w} C{dec_in_c} convT operand")
             self.conv(self.fwd_list, L.CONVT_FWD, lv.in_op, N, dec_h, dec_w, dec_in_c, lv.wup, lv.cat, lv.c_buf,
@@ -544,7 +544,9 @@ class Workspace:
             self.bn_forward(lv.bnA)
             lv.a1 = self.lazy(lv.zc1, co, lv.bnA.scale, lv.bnA.shift, act=L.ACT_RELU)
             lv.a1_op = lv.a1
-            if tma and tma_takes_3x3(lv.w, co):
+            # (256 px rows with <= 64 channels: the forward conv stays on the rolling-row engine, but the packed-tap
+            #  TMA weight gradient needs a plain operand and is 2x faster than the loader-warp one)
+            if tma and (tma_takes_3x3(lv.w, co) or (lv.w == 256 and co <= 64 and co % 8 == 0)):
                 lv.a1_op = self.materialize_act(lv.a1, lv.rows, co, lv.h * lv.w, f"{N}x{lv.h}x{lv.w} C{co} conv operand")
             self.conv(self.fwd_list, L.CONV_3X3, lv.a1_op, N, lv.h, lv.w, co, lv.wB, lv.zc2, co, bias=dcv[3].bias,
                       stats=self.stats_f(lv.bnB), stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)

@@ -21,10 +21,7 @@
 // Roles: warps 0-14 producers (the in-place transforms are issue-latency bound: 7 producer warps left the SM's four
 // schedulers half empty and a ring slot took ~6k cycles whatever its length), warp 15 MMA issuer (converged warp,
 // elected lane); when the stream ends producer warps 0-7 become the epilogue.
-#include <cuda.h>
-
 #include <cstdlib>
-#include <cstring>
 
 #include "conv_common.cuh"
 #include "stream_common.cuh"
@@ -60,7 +57,6 @@ struct WPlan {
   int g_lbo;           // 3x3: 0 = G slot has 2 chunks; else G slot has 1 chunk and the upper lanes read the zero chunk
   int RU, HS, WS, units, ctas_per_slice;
   int children, lw;    // transposed conv: 4 children (2x2 output positions), each its own CTA set; lw = log2(W)
-  int tma;             // 3x3 with PLAIN operands: rows are fetched by TMA boxes (one lane), no loader warps, no transform
 };
 
 struct WUnit {
@@ -98,9 +94,7 @@ struct WCursor {
 };
 
 template <int TAPS, bool CT>   // CT: 2x2 transposed conv (1x1 path with strided gradient rows, four children)
-__global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPlan K,
-                                                               const __grid_constant__ CUtensorMap tmA,
-                                                               const __grid_constant__ CUtensorMap tmG) {
+__global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPlan K) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -137,7 +131,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
   }
 
   if (tid == 0) {
-    for (int s = 0; s < K.ringA; ++s) { mbar_init(&full[s], K.tma ? 1 : SW_PROD_WARPS); mbar_init(&emptyA[s], 1); }
+    for (int s = 0; s < K.ringA; ++s) { mbar_init(&full[s], SW_PROD_WARPS); mbar_init(&emptyA[s], 1); }
     for (int s = 0; s < K.ringG; ++s) mbar_init(&emptyG[s], 1);
     mbar_init(done, 1);
     fence_barrier_init();
@@ -168,43 +162,7 @@ __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPla
     }
   };
 
-  if (TAPS == 9 && K.tma && warp < SW_PROD_WARPS) {
-    // ================================================================== TMA producer (plain operands): one lane
-    // fetches every A row segment (lines + 2 halo pixels, zero fill outside the image) and G row as boxes of 64
-    // channels straight into the swizzled ring slots; the other loader warps have nothing to do until the epilogue
-    if (warp == 0 && elect_one()) {
-      int ia = 0, ig = 0;
-      uint32_t pha = 0, phg = 0;
-      bool wrapA = false, wrapG = false;
-      const uint32_t abytes = (uint32_t)(K.a_lines * 128), gbytes = (uint32_t)(K.lines * 128);
-      WCursor c;
-      cur_init(c);
-      while (c.ok) {
-        const bool gok = c.j >= 1 && c.j <= c.ug.rows;
-        if (wrapA) mbar_wait(&emptyA[ia], pha);
-        if (gok && wrapG) mbar_wait(&emptyG[ig], phg);
-        const uint32_t bytes = abytes + (gok ? (K.g_lbo ? gbytes : 2 * gbytes) : 0u);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&full[ia])), "r"(bytes) : "memory");
-        const int hr = c.ug.h0 - 1 + c.j;
-        auto load4 = [&](uint32_t dst, const CUtensorMap* map, int c0, int x, int y) {
-          asm volatile(
-              "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, "
-              "%6}], [%2];"
-              ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(&full[ia])), "r"(c0), "r"(x), "r"(y), "r"(c.ug.n)
-              : "memory");
-        };
-        load4(ringA_u32 + (uint32_t)(ia * K.a_slot), &tmA, a_c0, c.ug.w0 - 1, hr);
-        if (gok) {
-          const uint32_t sG = ringG_u32 + (uint32_t)(ig * K.g_slot);
-          load4(sG, &tmG, g_c0, c.ug.w0, hr);
-          if (!K.g_lbo) load4(sG + (uint32_t)K.g_stride, &tmG, g_c0 + 64, c.ug.w0, hr);
-        }
-        cur_next(c);
-        if (++ia == K.ringA) { ia = 0; if (wrapA) pha ^= 1u; wrapA = true; }
-        if (gok && ++ig == K.ringG) { ig = 0; if (wrapG) phg ^= 1u; wrapG = true; }
-      }
-    }
-  } else if (warp < SW_PROD_WARPS) {
+  if (warp < SW_PROD_WARPS) {
     // ================================================================== producers
     const bf16* a_ptr = reinterpret_cast<const bf16*>(P.a.raw);
     const int a_ld = (int)P.a.ld;
@@ -664,29 +622,9 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     }
     attr_set = true;
   }
-  CUtensorMap tmA, tmG;
-  memset(&tmA, 0, sizeof(tmA));
-  memset(&tmG, 0, sizeof(tmG));
-  WgradArgs A2 = A;
-  // 3x3 with plain operands (a stored activation / concat buffer and a materialised gradient): rows by TMA
-  const bool plain = !A.a.scale && !A.a.gate && A.a.act == S2LC_ACT_NONE && !A.g.z && !A.g.rowscale;
-  if (K.taps == 9 && plain && !(debug_flags() & DBG_NO_TMA)) {
-    const uint64_t W = (uint64_t)A.W, H = (uint64_t)A.H, N = (uint64_t)A.N, lda = (uint64_t)A.a.ld, ldg = (uint64_t)A.g.ld_dy;
-    const uint64_t da[4] = {(uint64_t)A.Cin, W, H, N}, sa[3] = {lda, W * lda, H * W * lda};
-    const uint64_t dg[4] = {(uint64_t)A.Cout, W, H, N}, sg[3] = {ldg, W * ldg, H * W * ldg};
-    const uint32_t boxa[4] = {64, (uint32_t)K.a_lines, 1, 1}, boxg[4] = {64, (uint32_t)K.lines, 1, 1};
-    if (make_tma_map_bf16(&tmA, A.a.raw, 4, da, sa, boxa) && make_tma_map_bf16(&tmG, A.g.dy, 4, dg, sg, boxg)) {
-      K.tma = 1;
-      if (A.dbias) {   // the loader warps summed the bias gradient while transforming G; with TMA it is its own pass
-        launch_colsum_bf16(A.g.dy, A.g.ld_dy, M, A.Cout, A.dbias, st);
-        A2.dbias = nullptr;
-      }
-    }
-  }
-  if (K.taps == 9) swgrad_kernel<9, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A2, K, tmA, tmG);
-  else if (children == 4) swgrad_kernel<1, true><<<ctas * K.nsplit * K.children, SW_THREADS, smem, st>>>(A2, K, tmA, tmG);
-  else swgrad_kernel<1, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A2, K, tmA, tmG);
-  if (K.tma) note_tma_launch();
+  if (K.taps == 9) swgrad_kernel<9, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
+  else if (children == 4) swgrad_kernel<1, true><<<ctas * K.nsplit * K.children, SW_THREADS, smem, st>>>(A, K);
+  else swgrad_kernel<1, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
   return check_launch("swgrad_tc");
 }
 

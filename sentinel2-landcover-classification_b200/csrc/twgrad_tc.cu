@@ -38,6 +38,10 @@ struct GPlan {
   int kchunks, cps;     // 64-pixel chunks in total / per split
   int bw, bh, tiles_x, tiles_y;
   int stages, stage_bytes, tmem_cols;
+  int npack;            // > 1: the N operand is `npack` boxes of <= 64 channels each, one per x-shift of a 3x3 tap row
+                        // (3) or per child of a transposed conv (4): ONE wide MMA per k-step instead of 3 / 4 narrow
+                        // ones (a tcgen05.mma costs ~85 cycles however narrow it is: thin layers are bound by the count)
+  int mboxes;           // boxes of the M operand that exist (1 when it has <= 64 channels)
 };
 
 __device__ __forceinline__ void tg_expect_tx(uint64_t* bar, uint32_t bytes) {
@@ -118,7 +122,9 @@ __global__ void __launch_bounds__(TG_THREADS, 1) twgrad_kernel(WgradArgs P, GPla
         const int c_begin = I.ks * K.cps;
         const int c_end = min(c_begin + K.cps, K.kchunks);
         // tap geometry: 3x3 shifts the A box, a transposed conv selects the (qy, qx) phase of the G box
-        const int dy = K.kind == 1 ? I.tap / 3 - 1 : 0, dx = K.kind == 1 ? I.tap - (I.tap / 3) * 3 - 1 : 0;
+        // (packed: a 3x3 item is a whole tap ROW dy, a transposed-conv item covers all four children)
+        const int dy = K.kind == 1 ? (K.npack > 1 ? I.tap - 1 : I.tap / 3 - 1) : 0;
+        const int dx = (K.kind == 1 && K.npack == 1) ? I.tap - (I.tap / 3) * 3 - 1 : 0;
         const int qy = I.tap >> 1, qx = I.tap & 1;
         for (int c = c_begin; c < c_end; ++c) {
           int n = 0, y0 = 0, x0 = 0;
@@ -130,7 +136,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) twgrad_kernel(WgradArgs P, GPla
             x0 = (r - ty * K.tiles_x) * K.bw;
           }
           mbar_wait(&empty[s], ph ^ 1u);
-          tg_expect_tx(&full[s], (uint32_t)K.stage_bytes);
+          tg_expect_tx(&full[s], (uint32_t)((K.mboxes + K.NBc) * TG_CHUNK));
           const uint32_t sa = smem_base + (uint32_t)(s * K.stage_bytes);
           // one box of operand `g` (1 = gradient, 0 = activation) starting at channel c0
           auto box = [&](uint32_t dst, const CUtensorMap* map, bool g, int c0) {
@@ -144,9 +150,17 @@ __global__ void __launch_bounds__(TG_THREADS, 1) twgrad_kernel(WgradArgs P, GPla
             }
           };
           box(sa, mapM, K.m_on_g != 0, I.mt * 128);
-          box(sa + TG_CHUNK, mapM, K.m_on_g != 0, I.mt * 128 + 64);
-          for (int j = 0; j < K.NBc; ++j)
-            box(sa + 2 * TG_CHUNK + (uint32_t)(j * TG_CHUNK), mapN, K.m_on_g == 0, I.nt * K.NB + j * 64);
+          if (K.mboxes > 1) box(sa + TG_CHUNK, mapM, K.m_on_g != 0, I.mt * 128 + 64);
+          if (K.npack == 1) {
+            for (int j = 0; j < K.NBc; ++j)
+              box(sa + 2 * TG_CHUNK + (uint32_t)(j * TG_CHUNK), mapN, K.m_on_g == 0, I.nt * K.NB + j * 64);
+          } else if (K.kind == 1) {     // N = activation at x-shifts -1, 0, +1 (out-of-bounds columns are zero-filled)
+            for (int j = 0; j < 3; ++j)
+              tg_load_4d(sa + 2 * TG_CHUNK + (uint32_t)(j * TG_CHUNK), mapN, &full[s], 0, x0 + j - 1, y0 + dy, n);
+          } else {                      // N = gradient of the four children (qy, qx) of a transposed conv
+            for (int j = 0; j < 4; ++j)
+              tg_load_5d(sa + 2 * TG_CHUNK + (uint32_t)(j * TG_CHUNK), mapN, &full[s], 0, j & 1, x0, j >> 1, n * P.H + y0);
+          }
           if (++s == K.stages) { s = 0; ph ^= 1u; }
         }
       }
@@ -199,6 +213,7 @@ __global__ void __launch_bounds__(TG_THREADS, 1) twgrad_kernel(WgradArgs P, GPla
       const int mch = I.mt * 128 + r;
       const int tap3 = K.kind == 1 ? I.tap : 0;
       const int ct_base = K.kind == 2 ? I.tap * P.Cout : 0;
+      const int packed = K.npack > 1;
       mbar_wait(&acc_full[b], bph);
       tc_fence_after();
       for (int cj = half; cj < nchunks; cj += 2) {
@@ -207,8 +222,16 @@ __global__ void __launch_bounds__(TG_THREADS, 1) twgrad_kernel(WgradArgs P, GPla
         if (mch < K.CM) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int nch = I.nt * K.NB + cj * 16 + j;
-            if (nch < K.CN) {
+            int nch = I.nt * K.NB + cj * 16 + j;
+            if (packed) {
+              // column = (box jb, channel nch of the N side): jb is the x-shift of tap (dy, jb) or the child index
+              const int jb = nch >> 6;
+              nch &= 63;
+              if (nch < K.CN) {
+                if (K.kind == 1) atomicAdd(P.dw + wgrad_index(P, mch, (I.tap * 3 + jb) * P.Cin + nch), v[j]);
+                else atomicAdd(P.dw + wgrad_index(P, jb * P.Cout + nch, mch), v[j]);
+              }
+            } else if (nch < K.CN) {
               const int co = K.m_on_g ? mch : nch, ci = K.m_on_g ? nch : mch;
               atomicAdd(P.dw + wgrad_index(P, ct_base + co, tap3 * P.Cin + ci), v[j]);
             }
@@ -308,9 +331,12 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
   if (A.mode != S2LC_CONV_1X1 && A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONVT_FWD) return 1;
   // PLAIN operands only
   if (A.a.scale || A.a.gate || A.a.act != S2LC_ACT_NONE || A.g.z || A.g.rowscale) return 1;
-  if (A.Cin % 8 != 0 || A.Cout % 8 != 0 || A.a.ld % 8 != 0 || A.g.ld_dy % 8 != 0 || !tg_aligned16(A.a.raw) ||
+  // (the channel COUNTS may be anything: the tensor maps carry them as extents and zero-fill beyond; rows must start on
+  //  16 B boundaries)
+  if (A.a.ld % 8 != 0 || A.g.ld_dy % 8 != 0 || A.a.ld < A.Cin || A.g.ld_dy < A.Cout || !tg_aligned16(A.a.raw) ||
       !tg_aligned16(A.g.dy))
     return 1;
+  if (A.dbias && A.Cout % 8 != 0) return 1;       // the bias-gradient pass reads 8-channel vectors
   const bool take_all = (dbg & DBG_TMA_ALL) != 0;
   const int HW = A.H * A.W;
   const int cmin = A.Cin < A.Cout ? A.Cin : A.Cout;
@@ -321,9 +347,9 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
   // compute-bound; the shallow, HBM-bound layers belong to the rolling-row engine (swgrad_tc.cu)
   if (!take_all) {
     // (tools/tma_wgrad_sweep.sh, profiles/r02c_tma_wgrad_sweep.txt: 3x3 at 128 px is a tie, at 256 px a loss)
-    if (K.kind == 1 && HW > 64 * 64) return 1;
+    if (K.kind == 1 && HW > 64 * 64 && !(A.Cin <= 64 && A.Cin % 8 == 0 && A.Cout <= 128 && A.W <= 256)) return 1;   // thin layers: packed taps
     if (K.kind == 0 && (HW > 64 * 64 || cmin < 64)) return 1;
-    if (K.kind == 2 && (HW > 128 * 128 || cmin < 64)) return 1;
+    if (K.kind == 2 && (HW > 128 * 128 || cmin < 64) && !(A.Cout <= 64 && A.Cin <= 128)) return 1;
   }
   const int64_t M = (int64_t)A.N * HW;
   if (M >= (1ll << 31) / 4) return 1;
@@ -340,14 +366,25 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
     K.kchunks = (int)((M + 63) / 64);
   }
   K.m_on_g = A.Cout >= A.Cin ? 1 : 0;
+  K.npack = 1;
+  // thin layers: pack the x-shifts of a tap row (3x3, <= 64 input channels) or the four children (transposed conv,
+  // <= 64 output channels) along N
+  // (Cin a multiple of 8: a 38-channel slice of a 40-wide concat buffer measured slower than the rolling-row engine)
+  if (K.kind == 1 && A.Cin <= 64 && A.Cin % 8 == 0 && A.Cout <= 128) { K.npack = 3; K.m_on_g = 1; K.taps = 3; }
+  if (K.kind == 2 && A.Cout <= 64 && A.Cin <= 128) { K.npack = 4; K.m_on_g = 0; K.taps = 1; }
   K.CM = K.m_on_g ? A.Cout : A.Cin;
   K.CN = K.m_on_g ? A.Cin : A.Cout;
   K.m_tiles = (K.CM + 127) / 128;
-  const int n16 = (K.CN + 15) / 16 * 16;
-  const int nt = (n16 + 255) / 256;
-  K.NB = ((n16 + nt - 1) / nt + 15) / 16 * 16;
-  K.n_tiles = (K.CN + K.NB - 1) / K.NB;
-  K.NBc = (K.NB + 63) / 64;
+  K.mboxes = K.CM > 64 ? 2 : 1;
+  if (K.npack > 1) {
+    K.NB = K.npack * 64; K.n_tiles = 1; K.NBc = K.npack;
+  } else {
+    const int n16 = (K.CN + 15) / 16 * 16;
+    const int nt = (n16 + 255) / 256;
+    K.NB = ((n16 + nt - 1) / nt + 15) / 16 * 16;
+    K.n_tiles = (K.CN + K.NB - 1) / K.NB;
+    K.NBc = (K.NB + 63) / 64;
+  }
   K.stage_bytes = (2 + K.NBc) * TG_CHUNK;
   const int fixed = 1024 + (2 * TG_MAX_STAGES + 4) * 8 + 64;
   K.stages = (226 * 1024 - fixed) / K.stage_bytes;
@@ -360,7 +397,7 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
   const int sms = kNumSMs;
   int best_ks = 1;
   long best_cost = -1;
-  for (int ks = 1; ks <= 32 && ks <= K.kchunks; ++ks) {
+  for (int ks = 1; ks <= 160 && ks <= K.kchunks; ++ks) {
     const int cps = (K.kchunks + ks - 1) / ks;
     if (ks > 1 && cps < 4) break;
     const long waves = ((long)items0 * ks + sms - 1) / sms;

@@ -128,7 +128,9 @@ from test_gpu_kernels import run_wgrad  # noqa: E402
 DW_TOL = 1e-3
 
 W3 = [(640, 512, 2, 32, 32), (512, 512, 1, 32, 32), (320, 256, 2, 64, 64), (256, 256, 1, 40, 64), (40, 32, 3, 16, 16),
-      (72, 200, 2, 8, 16), (168, 128, 1, 24, 128)]
+      (72, 200, 2, 8, 16), (168, 128, 1, 24, 128),
+      # thin layers: the three x-shifts of a tap row packed along N
+      (32, 32, 1, 70, 256), (40, 32, 2, 12, 128), (64, 64, 1, 72, 256), (24, 128, 2, 16, 64)]
 
 
 @pytest.mark.parametrize("cin,cout,n,h,w", W3)
@@ -160,7 +162,7 @@ def test_tma_wgrad1x1(lib, cin, cout, n, h, w):
 
 
 @pytest.mark.parametrize("cin,cout,n,h,w", [(2048, 512, 4, 16, 16), (512, 256, 2, 32, 32), (256, 128, 2, 64, 64),
-                                            (64, 32, 1, 8, 16)])
+                                            (64, 32, 1, 8, 16), (64, 32, 2, 40, 64), (128, 64, 1, 24, 128), (40, 48, 2, 8, 16)])
 def test_tma_wgradT(lib, cin, cout, n, h, w):
     rows = n * h * w
     x = mk((rows, cin), 361).to(BF)
@@ -172,25 +174,3 @@ def test_tma_wgradT(lib, cin, cout, n, h, w):
     ref = torch.einsum("nihw,nohywx->ioyx", nchw(x, n, h, w), g6)
     assert rel_err(dw, ref) < DW_TOL
     assert rel_err(db, nchw(g, n, 2 * h, 2 * w).sum((0, 2, 3))) < DW_TOL
-
-
-@pytest.mark.parametrize("cin,cout,n,h,w", [(32, 32, 1, 70, 256), (38, 32, 2, 12, 128), (88, 64, 2, 10, 128), (64, 64, 1, 72, 256),
-                                            (128, 128, 2, 130, 128), (168, 128, 1, 72, 128)])
-def test_tma_streaming_wgrad3x3(lib, cin, cout, n, h, w):
-    """The rolling-row weight-gradient engine (csrc/swgrad_tc.cu) with its TMA producer: wide, shallow 3x3 layers with
-    plain operands (production dispatch: the take-all flag of this file is cleared, so twgrad_tc declines > 64 px)."""
-    old = lib.s2lc_set_debug_flags(0)
-    try:
-        rows = n * h * w
-        cb = (cin + 7) // 8 * 8
-        x = mk((rows, cb), 371).to(BF)
-        x[:, cin:] = 0
-        g = mk((rows, cout), 372).to(BF)
-        dw = torch.zeros(cout, cin, 3, 3, device="cuda")
-        db = torch.zeros(cout, device="cuda")
-        took_tma(lib, lambda: run_wgrad(lib, 1, 1, lazy(x, cb), lazygrad(g, cout), n, h, w, cin, cout, dw, db))
-        ref = torch.nn.grad.conv2d_weight(nchw(x, n, h, w)[:, :cin], (cout, cin, 3, 3), nchw(g, n, h, w), padding=1)
-        assert rel_err(dw, ref) < DW_TOL
-        assert rel_err(db, nchw(g, n, h, w).sum((0, 2, 3))) < DW_TOL
-    finally:
-        lib.s2lc_set_debug_flags(old)
