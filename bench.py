@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--mode", default="train", choices=["train", "infer"],
                     help="train: BASELINE.json configs[1-3] (the headline); infer: configs[4], forward-only mosaic predict")
+    ap.add_argument("--ref-batch", type=int, default=1,
+                    help="--impl reference: tiles per CPU step (BASELINE.md section 4 rows; the driver's arm uses 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true")
     ap.add_argument("--no-breakdown", action="store_true")
@@ -134,7 +136,7 @@ def run_reference(a) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    bs = 1   # bounded sample: one 512x512 tile per step of the same workload
+    bs = max(int(a.ref_batch), 1)   # bounded sample: one tile per step of the same workload unless --ref-batch says more
     # all the host cores this process may use (torchrun exports OMP_NUM_THREADS=1 for its workers)
     try:
         ncpu = len(os.sched_getaffinity(0))
@@ -154,7 +156,7 @@ def run_reference(a) -> None:
     v = bs / dt
     cores = torch.get_num_threads()
     what = "eval forward + argmax" if infer else "fwd+focal+bwd+Adam"
-    sample = f"{a.steps} steps of 1 tile {a.size}x{a.size} fp32 {what} (oracle port of the reference modules)"
+    sample = f"{a.steps} steps of {bs} tile(s) {a.size}x{a.size} fp32 {what} (oracle port of the reference modules)"
     emit({
         "impl": "reference", "metric": "infer_tiles_per_s" if infer else "train_tiles_per_s", "value": v, "unit": "tiles/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
