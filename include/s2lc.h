@@ -132,6 +132,11 @@ int32_t s2lc_weight_pack(const float* src, void* dst, int32_t dtype, int32_t N1,
  * replaces efficientnet_unet.py:191-194 (+ the TF-"same" pad of :288-297); writes raw NHWC + moments */
 int32_t s2lc_stem_conv_fwd(const float* x_nchw, const float* w_oihw, void* out, double* stats, int32_t N, int32_t Cin,
                            int32_t H, int32_t W, int32_t Co, int32_t dtype, void* stream);
+/* im2col of the stem for the bf16 production path: cols[(n, oy, ox), ci*9 + ty*3 + tx] (zero up to `ld` columns), so
+ * that Conv2dSamePadding(k=3, s=2) (efficientnet_unet.py:191-194, :288-297) and its weight gradient run as K = 56
+ * contractions on the tensor-core engines (s2lc_conv_fwd / s2lc_conv_wgrad in 1x1 mode on the column buffer). */
+int32_t s2lc_stem_im2col(const float* x_nchw, void* cols, int64_t ld, int32_t N, int32_t Cin, int32_t H, int32_t W,
+                         int32_t dtype, void* stream);
 int32_t s2lc_stem_conv_wgrad(const float* x_nchw, const s2lc_lazygrad* g, float* dw_oihw, int32_t N, int32_t Cin,
                              int32_t H, int32_t W, int32_t Co, int32_t dtype, void* stream);
 

@@ -400,9 +400,23 @@ class Workspace:
         c0 = stem_conv.out_channels
         z0 = self.act(N * h0 * w0, c0)
         bn0 = _BN(self, stem_bn_mod, N * h0 * w0)
-        self.F("s2lc_stem_conv_fwd", self.x_ptr, stem_conv.weight.data_ptr(), z0.data_ptr(), self.stats_f(bn0), N,
-               cfg.in_channels, H, W, c0, self.dt)
-        self.meta(self.fwd_meta, N * cfg.in_channels * H * W * 4 + N * h0 * w0 * c0 * self.es, 2.0 * N * h0 * w0 * c0 * 9 * cfg.in_channels)
+        k_stem = 9 * cfg.in_channels
+        stem_tc = tma and k_stem <= 64
+        if stem_tc:
+            # bf16 production path: im2col once (kept for the weight gradient), then a K = 56 contraction on the
+            # tensor-core engines; the direct CUDA-core kernels below ran at 0.43 TB/s (0.93 + 1.08 ms per step)
+            self.stem_cols = self.act(N * h0 * w0, 64)
+            self.F("s2lc_stem_im2col", self.x_ptr, self.stem_cols.data_ptr(), 64, N, cfg.in_channels, H, W, self.dt,
+                   nbytes=N * cfg.in_channels * H * W * 4 + N * h0 * w0 * 64 * self.es)
+            self.stem_lazy = self.lazy(self.stem_cols, 64)
+            w_stem = pk("encoder.stem.0/f", lambda: PackedWeight(stem_conv.weight, dt, 1, c0, 1, k_stem, 0, k_stem, 0, 1))
+            self.conv(self.fwd_list, L.CONV_1X1, self.stem_lazy, N, h0, w0, _up(k_stem, 8), w_stem, z0, c0,
+                      stats=self.stats_f(bn0), stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)
+            self.fwd_meta[-1][0] = "stem_conv_fwd"
+        else:
+            self.F("s2lc_stem_conv_fwd", self.x_ptr, stem_conv.weight.data_ptr(), z0.data_ptr(), self.stats_f(bn0), N,
+                   cfg.in_channels, H, W, c0, self.dt)
+            self.meta(self.fwd_meta, N * cfg.in_channels * H * W * 4 + N * h0 * w0 * c0 * self.es, 2.0 * N * h0 * w0 * c0 * 9 * cfg.in_channels)
         self.bn_forward(bn0)
         cur = self.lazy(z0, c0, bn0.scale, bn0.shift, act=L.ACT_SILU)   # lazy stem output
         cur_h, cur_w = h0, w0
@@ -740,8 +754,12 @@ class Workspace:
                 self.meta(self.bwd_meta, dw_bytes, dw_flops, desc=bd)
                 self.bn_backward(bn0, "encoder.stem.1")
                 g0 = self.lazygrad(dy0, c0, z0, c0, bn0)
-                self.B("s2lc_stem_conv_wgrad", self.x_ptr, C.byref(g0), self.gptr("encoder.stem.0.weight"), N,
-                       cfg.in_channels, H, W, c0, self.dt)
+                if stem_tc:
+                    self.wgrad(L.CONV_1X1, self.stem_lazy, g0, N, h0, w0, k_stem, c0, self.gptr("encoder.stem.0.weight"))
+                    self.bwd_meta[-1][0] = "stem_conv_wgrad"
+                else:
+                    self.B("s2lc_stem_conv_wgrad", self.x_ptr, C.byref(g0), self.gptr("encoder.stem.0.weight"), N,
+                           cfg.in_channels, H, W, c0, self.dt)
         self.stats_b_arena = torch.zeros(max(self._stats_b_total, 1), dtype=torch.float64, device=self.dev)
         self._resolve()
 

@@ -57,6 +57,7 @@ _PROTOS = {
     "s2lc_memset_zero": ([vp, i64, vp], i32),
     "s2lc_weight_pack": ([vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i32, vp], i32),
     "s2lc_stem_conv_fwd": ([vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp], i32),
+    "s2lc_stem_im2col": ([vp, vp, i64, i32, i32, i32, i32, i32, vp], i32),
     "s2lc_stem_conv_wgrad": ([vp, C.POINTER(LazyGrad), vp, i32, i32, i32, i32, i32, i32, vp], i32),
     "s2lc_bn_finalize": ([vp, vp, vp, f64, f32, f32, vp, vp, vp, vp, vp, vp, i32, vp], i32),
     "s2lc_bn_eval_affine": ([vp, vp, vp, vp, f32, vp, vp, i32, vp], i32),

@@ -562,6 +562,14 @@ __global__ void nchw_to_slice_kernel(const float* __restrict__ x, T* __restrict_
   int64_t HW = (int64_t)H * W, total = (int64_t)N * HW;
   for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < total; r += (int64_t)gridDim.x * blockDim.x) {
     int64_t n = r / HW, hw = r % HW;
+    if (sizeof(T) == 2 && Cfill == 8 && ((reinterpret_cast<uintptr_t>(dst + r * ld_dst) & 15) == 0)) {
+      // the usual case (6 bands into an 8-channel slice of the concat buffer): one 16 B store per pixel
+      float v[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) v[c] = c < C ? __ldg(x + (n * C + c) * HW + hw) : 0.f;
+      Vec8<T>::store(dst + r * ld_dst, v);
+      continue;
+    }
     for (int c = 0; c < Cfill; ++c) {
       float v = c < C ? x[(n * C + c) * HW + hw] : 0.f;
       stf<T>(dst + r * ld_dst + c, v);
