@@ -36,7 +36,8 @@ constexpr int TV_MAX_STAGES = 8;
 constexpr int TV_A_BYTES = 128 * 128;   // 128 pixels x 64 channels bf16
 
 struct TPlan {
-  int taps;          // 1 or 9
+  int taps;          // 1, 9 (3x3) or 4 (data gradient of a 2x2 stride-2 transposed conv)
+  int boxed;         // 1: a tile is a pixel BOX (bw x bh) of one sample (3x3, ConvT data gradient); 0: 128 consecutive pixels
   int KC;            // 64-channel chunks per tap
   int ksteps_last;   // K = 16 steps in the last chunk of a tap (1..4)
   int BN;            // output columns per tile (multiple of 16, <= 256)
@@ -67,6 +68,14 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, "
+      "%7}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
@@ -82,7 +91,7 @@ __device__ __forceinline__ TTile tile_of(const ConvArgs& P, const TPlan& K, int 
   T.nt = t - T.mt * K.n_tiles;
   T.n = 0; T.y0 = 0; T.x0 = 0;
   T.m0 = (int64_t)T.mt * 128;
-  if (K.taps == 9) {
+  if (K.boxed) {
     const int per = K.tiles_x * K.tiles_y;
     T.n = T.mt / per;
     const int r = T.mt - T.n * per;
@@ -158,6 +167,8 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
             mbar_expect_tx(&full[s], bytes);
             const uint32_t sa = smem_base + (uint32_t)(s * K.stage_bytes);
             if (K.taps == 9) tma_load_4d(sa, &tmA, &full[s], kc * 64, T.x0 + dx, T.y0 + dy, T.n);
+            else if (K.taps == 4)   // child (qy, qx) = tap of the 2H x 2W gradient, viewed as (c, qx, w, qy, n*H + h)
+              tma_load_5d(sa, &tmA, &full[s], kc * 64, tap & 1, T.x0, tap >> 1, T.n * P.H + T.y0);
             else tma_load_2d(sa, &tmA, &full[s], kc * 64, (int)T.m0);
             tma_load_2d(sa + TV_A_BYTES, &tmB, &full[s], tap * P.Cpad + kc * 64, n0);
             if (++s == K.stages) { s = 0; ph ^= 1u; }
@@ -241,7 +252,7 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
         const TTile T = tile_of(P, K, t);
         const int n0 = T.nt * K.BN;
         int rows_valid = 128;
-        if (K.taps != 9) {
+        if (!K.boxed) {
           const int64_t left = M - T.m0;
           rows_valid = left < 128 ? (int)left : 128;
         }
@@ -294,7 +305,7 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
         if (etid == 0) {
           for (int j = 0; j < boxes; ++j) {
             if (n0 + j * 64 >= P.Nout) break;
-            if (K.taps == 9) tma_store_4d(&tmO, ost + (uint32_t)(j * 16384), n0 + j * 64, T.x0, T.y0, T.n);
+            if (K.boxed) tma_store_4d(&tmO, ost + (uint32_t)(j * 16384), n0 + j * 64, T.x0, T.y0, T.n);
             else tma_store_2d(&tmO, ost + (uint32_t)(j * 16384), n0 + j * 64, (int)T.m0);
           }
           tma_store_commit();
@@ -330,7 +341,7 @@ __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan 
       int64_t m;
       int sn, ph_, pw_;
       bool valid = true;
-      if (K.taps == 9) {
+      if (K.boxed) {
         ph_ = T.y0 + (r >> K.bw_shift);
         pw_ = T.x0 + (r & (K.bw - 1));
         sn = T.n;
@@ -559,8 +570,8 @@ static bool tv_make_map(CUtensorMap* map, const void* base, int rank, const uint
                         const uint32_t* box) {
   TmapEncodeFn enc = tmap_encode_fn();
   if (!enc) return false;
-  cuuint64_t gdim[4], gstr[3];
-  cuuint32_t bx[4], es[4];
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bx[5], es[5];
   for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_el[i] * 2;
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
@@ -574,7 +585,7 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
   const uint32_t dbg = debug_flags();
   if (dbg & (DBG_NO_TMA | DBG_NO_STREAM)) return 1;
   if (A.dtype != S2LC_BF16) return 1;
-  if (A.mode != S2LC_CONV_1X1 && A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONVT_FWD) return 1;
+  if (A.mode != S2LC_CONV_1X1 && A.mode != S2LC_CONV_3X3 && A.mode != S2LC_CONVT_FWD && A.mode != S2LC_CONVT_DGRAD) return 1;
   // PLAIN operand only: a stored tensor, nothing to apply on the way to the tensor core
   const void* a_ptr;
   int64_t a_ld;
@@ -594,7 +605,8 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
   const int64_t M = (int64_t)A.N * A.H * A.W;
   if (M >= (1ll << 31)) return 1;
   TPlan K{};
-  K.taps = A.mode == S2LC_CONV_3X3 ? 9 : 1;
+  K.taps = A.mode == S2LC_CONV_3X3 ? 9 : (A.mode == S2LC_CONVT_DGRAD ? 4 : 1);
+  K.boxed = K.taps != 1;
   K.KC = (A.C + 63) / 64;
   K.ksteps_last = (A.C - (K.KC - 1) * 64 + 15) / 16;
   // Which plain shapes this engine takes (tools/tma_sweep.sh, profiles/r02b_tma_sweep.txt): 3x3 layers up to 128 px
@@ -611,8 +623,8 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
     if (A.mode == S2LC_CONV_1X1 && A.C < 176 && !(epi_ok && A.Nout >= 64)) return 1;
     if (A.mode == S2LC_CONVT_FWD && A.C < 128) return 1;
   }
-  if (K.taps == 9) {
-    if (!take_all && !(A.W <= 128 || (A.W == 256 && A.C > 64))) return 1;
+  if (K.boxed) {
+    if (K.taps == 9 && !take_all && !(A.W <= 128 || (A.W == 256 && A.C > 64))) return 1;
     K.bw = A.W < 128 ? A.W : 128;
     if ((K.bw & (K.bw - 1)) != 0 || K.bw < 8 || A.W % K.bw != 0) return 1;
     K.bh = 128 / K.bw;
@@ -668,6 +680,13 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
     const uint64_t str[3] = {(uint64_t)a_ld, (uint64_t)A.W * a_ld, (uint64_t)A.H * A.W * a_ld};
     const uint32_t box[4] = {64, (uint32_t)K.bw, (uint32_t)K.bh, 1};
     ok = tv_make_map(&tmA, a_ptr, 4, dims, str, box);
+  } else if (K.taps == 4) {
+    // the gradient lives at 2H x 2W: view (c, qx, w, qy, n*H + h), a tap is the phase (qy, qx)
+    const uint64_t W = (uint64_t)A.W, ld = (uint64_t)a_ld;
+    const uint64_t dims[5] = {(uint64_t)A.C, 2, W, 2, (uint64_t)A.N * A.H};
+    const uint64_t str[4] = {ld, 2 * ld, 2 * W * ld, 4 * W * ld};
+    const uint32_t box[5] = {64, 1, (uint32_t)K.bw, 1, (uint32_t)K.bh};
+    ok = tv_make_map(&tmA, a_ptr, 5, dims, str, box);
   } else {
     const uint64_t dims[2] = {(uint64_t)A.C, (uint64_t)M};
     const uint64_t str[1] = {(uint64_t)a_ld};
@@ -681,7 +700,7 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
     ok = ok && tv_make_map(&tmB, A.w_packed, 2, dims, str, box);
   }
   if (ok && K.epi_tma) {
-    if (K.taps == 9) {
+    if (K.boxed) {
       const uint64_t dims[4] = {(uint64_t)A.Nout, (uint64_t)A.W, (uint64_t)A.H, (uint64_t)A.N};
       const uint64_t str[3] = {(uint64_t)A.ld_out, (uint64_t)A.W * A.ld_out, (uint64_t)A.H * A.W * A.ld_out};
       const uint32_t box[4] = {64, (uint32_t)K.bw, (uint32_t)K.bh, 1};

@@ -174,3 +174,29 @@ def test_tma_wgradT(lib, cin, cout, n, h, w):
     ref = torch.einsum("nihw,nohywx->ioyx", nchw(x, n, h, w), g6)
     assert rel_err(dw, ref) < DW_TOL
     assert rel_err(db, nchw(g, n, 2 * h, 2 * w).sum((0, 2, 3))) < DW_TOL
+
+
+@pytest.mark.parametrize("cin,cout,n,h,w", [(2048, 512, 2, 16, 16), (512, 256, 2, 32, 32), (128, 64, 2, 128, 128),
+                                            (64, 32, 1, 24, 256), (40, 48, 2, 8, 16)])
+def test_tma_convT_dgrad(lib, cin, cout, n, h, w):
+    """Data gradient of ConvTranspose2d(k=2, s=2): each input pixel gathers its four children (phases of a 5-D TMA view
+    of the 2H x 2W gradient), act'(prev) epilogue, BNBWD statistics."""
+    rows = n * h * w
+    x = mk((rows, cin), 381).to(BF)
+    sc, sh = 1 + 0.1 * mk((cin,), 382), 0.1 * mk((cin,), 383)
+    wt = mk((cin, cout, 2, 2), 384, 1 / math.sqrt(4 * cout))
+    ccat = cout + 8
+    dcat = torch.zeros(rows * 4, ccat, dtype=BF, device="cuda")
+    dcat[:, :cout] = mk((rows * 4, cout), 385).to(BF)
+    pwd = pack(lib, wt, BF, 1, 1, cin, 4, cout, 0, cout * 4, 1, 4)
+    dx = torch.empty(rows, cin, dtype=BF, device="cuda")
+    st = torch.zeros(2 * cin, dtype=torch.float64, device="cuda")
+    took_tma(lib, lambda: run_conv(lib, 1, 3, lazygrad(dcat, ccat), n, h, w, cout, pwd, dx, cin,
+                                   prev=lazy(x, cin, sc, sh, act=2), stats=st, kind=2))
+    g = nchw(dcat, n, 2 * h, 2 * w)[:, :cout]
+    u = nchw(x, n, h, w) * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1)
+    want = F.conv2d(g, bfr(wt), stride=2) * act_bwd(u, 2)     # dgrad of convT(k=2, s=2) = strided conv with the same weight
+    gotx = nchw(dx, n, h, w)
+    assert rel_err(gotx, want) < OUT_TOL
+    assert rel_err(st[:cin], gotx.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(st[cin:], (gotx.double() * nchw(x, n, h, w).double()).sum((0, 2, 3))) < 1e-5
