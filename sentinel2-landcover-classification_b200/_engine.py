@@ -29,6 +29,11 @@ MATERIALIZE_DECODER_GRADS = os.environ.get("S2LC_MATERIALIZE", "1") != "0"
 TMA_OPERANDS = os.environ.get("S2LC_NO_TMA", "0") != "1"
 
 
+# MBConv blocks up to this many pixels per sample get their project-conv operand / BatchNorm-backward gradients
+# materialised (A/B knob: S2LC_TMA_BLOCK_HW; 128 x 128 measured 0.8 ms per step better than 64 x 64, 256 x 256 is a loss)
+TMA_BLOCK_HW = int(os.environ.get("S2LC_TMA_BLOCK_HW", str(128 * 128)))
+
+
 def tma_takes_3x3(width: int, c: int) -> bool:
     """Mirror of the shape rule in csrc/tconv_tc.cu launch_tconv_tc."""
     return width <= 128 or (width == 256 and c > 64)
@@ -474,7 +479,7 @@ class Workspace:
             rec.w3 = pack_1x1(rec.k3, conv3.weight)
             # project convs at <= 64 px: the gated operand is written once and fed by TMA (forward conv + weight gradient)
             rec.s2_op = rec.s2_gated
-            if tma and ho * wo <= 64 * 64:
+            if tma and ho * wo <= TMA_BLOCK_HW:
                 rec.s2_op = self.materialize_act(rec.s2_gated, rows_out, sp.c_exp, ho * wo, bd)
             self.conv(self.fwd_list, L.CONV_1X1, rec.s2_op, N, ho, wo, sp.c_exp, rec.w3, rec.z3, sp.c_out,
                       stats=self.stats_f(rec.bn3), stats_kind=L.STATS_MOMENTS if train else L.STATS_NONE)
@@ -686,7 +691,7 @@ class Workspace:
             bd = f"blk{i} {N}x{hi}x{wi} C{sp.c_exp} k{sp.kernel}s{sp.stride}"
             self.bn_backward(rec.bn3, rec.kbn3)
             g3 = self.lazygrad(dYi, sp.c_out, rec.z3, sp.c_out, rec.bn3, rowscale=dc_ptr(i))
-            if tma and ho * wo <= 64 * 64:
+            if tma and ho * wo <= TMA_BLOCK_HW:
                 # deep blocks: the BatchNorm-backward gradient is written once (out of place: dYi still feeds the
                 # residual path) and both gradient engines read it as a plain tensor, the data gradient through TMA
                 self.B("s2lc_lazygrad_apply", C.byref(g3), g3m_buf.data_ptr(), sp.c_out, rec.rows_out, sp.c_out,
@@ -722,7 +727,7 @@ class Workspace:
                 self.meta(self.bwd_meta, dw_bytes, dw_flops, desc=bd)
                 self.bn_backward(rec.bn1, rec.kbn1)
                 g1 = self.lazygrad(dy1_buf, sp.c_exp, rec.z1, sp.c_exp, rec.bn1)
-                if tma and hi * wi <= 64 * 64:
+                if tma and hi * wi <= TMA_BLOCK_HW:
                     g1 = self.materialize_grad(g1, dy1_buf, sp.c_exp, rec.rows_in, sp.c_exp, hi * wi)
                 self.wgrad(L.CONV_1X1, rec.x_lazy, g1, N, hi, wi, sp.c_in, sp.c_exp, self.gptr(rec.k1 + ".weight"))
                 if prev_rec is None:

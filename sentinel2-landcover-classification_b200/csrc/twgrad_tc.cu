@@ -348,7 +348,7 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
   if (!take_all) {
     // (tools/tma_wgrad_sweep.sh, profiles/r02c_tma_wgrad_sweep.txt: 3x3 at 128 px is a tie, at 256 px a loss)
     if (K.kind == 1 && HW > 64 * 64 && !(A.Cin <= 64 && A.Cin % 8 == 0 && A.Cout <= 128 && A.W <= 256)) return 1;   // thin layers: packed taps
-    if (K.kind == 0 && (HW > 64 * 64 || cmin < 64)) return 1;
+    if (K.kind == 0 && (HW > 128 * 128 || cmin < 32 || (HW > 64 * 64 && cmin < 32))) return 1;
     if (K.kind == 2 && (HW > 128 * 128 || cmin < 64) && !(A.Cout <= 64 && A.Cin <= 128)) return 1;
   }
   const int64_t M = (int64_t)A.N * HW;
