@@ -531,6 +531,15 @@ def main() -> None:
         if agg is not None:
             out["roofline"] = roofline_of(top, ws, hook["fwd"], hook["bwd"], a.steps, pk, pk_kind, ms)
             out["kernel_breakdown"] = breakdown_table(agg)
+            bt = getattr(kernel_breakdown, "best_tensor", None)
+            if bt is not None:   # the GEMM side of BASELINE.json's metric: the best tensor-core launch of the step
+                tpk = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+                out["tensor_roofline"] = {
+                    "bound": "tensor", "achieved": round(bt[0], 1), "peak": tpk, "unit": "TFLOP/s",
+                    "frac": round(bt[0] / tpk, 4), "kernel": bt[1], "layer": bt[2], "launch_ms": round(bt[3], 4),
+                    "algorithmic_flops": bt[4], "peak_source": pk_kind,
+                    "timing": "CUDA events around this one launch in the instrumented warm-up step (every other launch "
+                              "of the step is in kernel_breakdown); ncu: profiles/r02e_tconv3x3_32_ncu.txt"}
     if world == 1 and rank == 0:
         del trainer, model, eng, ws, bufs, x, y          # release the engine's HBM before the eager comparator
         if not a.no_gpu_baseline:
@@ -561,14 +570,21 @@ def kernel_breakdown(trainer, model, ws, x, y) -> dict:
     eng.bucket_hook = hook
     torch.cuda.synchronize()
     agg: dict[str, list] = {}
+    best = None     # fastest tensor-core launch of the step (TFLOP/s), for the `tensor_roofline` key
     for metas, evs in ((ws.fwd_meta, ev_f), (ws.bwd_meta, ev_b)):
         for e0, e1, i in evs:
             label, nbytes, flops, _desc = metas[i]
+            t = e0.elapsed_time(e1)
             r = agg.setdefault(label, [0, 0.0, 0.0, 0.0])
             r[0] += 1
-            r[1] += e0.elapsed_time(e1)
+            r[1] += t
             r[2] += nbytes
             r[3] += flops
+            if flops > 1e10 and t > 0 and label.startswith(("conv3x3", "conv1x1", "convT")):
+                tf = flops / t / 1e9
+                if best is None or tf > best[0]:
+                    best = (tf, label, _desc, t, flops)
+    kernel_breakdown.best_tensor = best
     return agg
 
 
@@ -581,13 +597,13 @@ def breakdown_table(agg: dict) -> list:
 
 
 # kernel-class label -> CUDA kernel behind it (for the ncu cross-reference in profiles/)
-KERNEL_OF = {"conv1x1_wgrad": "swgrad_kernel<1,false> (streaming; wgrad_tc_kernel for the shapes it declines)",
-             "conv3x3_wgrad": "swgrad_kernel<9,false> (streaming, every decoder level)",
-             "convT_wgrad": "swgrad_kernel<1,true> (streaming, four children)",
-             "conv3x3": "sconv_kernel<9,*> (W % 128 == 0) / conv_tc_kernel<2>",
-             "conv3x3_dgrad": "sconv_kernel<9,*> (W % 128 == 0) / conv_tc_kernel<2>",
-             "conv1x1": "sconv_kernel<1,*> (shallow) / conv_tc_kernel<2> (deep)",
-             "conv1x1_dgrad": "sconv_kernel<1,*> (shallow) / conv_tc_kernel<2> (deep)",
+KERNEL_OF = {"conv1x1_wgrad": "twgrad_kernel (TMA-fed, blocks <= 128 px) / swgrad_kernel<1,false> (streaming, shallow)",
+             "conv3x3_wgrad": "twgrad_kernel (TMA-fed, <= 64 px and packed taps at 256 px) / swgrad_kernel<9,false> (streaming)",
+             "convT_wgrad": "twgrad_kernel (TMA-fed, children packed along N for <= 64 output channels)",
+             "conv3x3": "tconv_kernel (TMA-fed, <= 128 px rows and 88->64 @256) / sconv_kernel<9,*> (streaming, 256 / 512 px)",
+             "conv3x3_dgrad": "tconv_kernel (TMA-fed, <= 128 px rows) / sconv_kernel<9,*> (streaming, 256 / 512 px)",
+             "conv1x1": "tconv_kernel (TMA-fed, every plain operand; TMA-store epilogue) / sconv_kernel<1,*> (lazy shallow operands)",
+             "conv1x1_dgrad": "tconv_kernel (TMA-fed, blocks <= 128 px) / sconv_kernel<1,*> (lazy shallow operands)",
              "dwconv_fwd": "dw2::dw2_fwd_kernel",
              "dwconv_bwd": "dw2::dw2_bwd_kernel (fused data + weight gradient)"}
 
