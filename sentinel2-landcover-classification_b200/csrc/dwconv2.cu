@@ -841,6 +841,7 @@ using namespace s2lc;
   if (s == 1) {                                          \
     if (wide) {                                          \
       if (k == 3) { if (half) DW2_F(s2lc::bf16, 3, 1, 4, 4, 2, 2, 32); DW2_F(s2lc::bf16, 3, 1, 4, 4, 2, 2, 64); } \
+      if (half5) DW2_F(s2lc::bf16, 5, 1, 4, 2, 2, 2, 32); \
       DW2_F(s2lc::bf16, 5, 1, 4, 2, 2, 2, 64);           \
     }                                                    \
     if (k == 3) DW2_F(s2lc::bf16, 3, 1, 2, 4, 3, 2, 64); \
@@ -867,6 +868,7 @@ int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* 
   const bool wide = W > 16;
   // 32-channel blocks: last 64-block at most half full, or rows >= 128 px (two pixel groups per warp are 5-10 % faster there)
   const bool half = W >= 64 && (((C + 63) % 64) < 32 || W >= 128 || (s2lc::debug_flags() & s2lc::DBG_DW_CB32));
+  const bool half5 = W >= 64;      // 5x5: 32-channel blocks are 5-8 % faster at 64 px rows (two pixel groups per warp)
   if (dtype == S2LC_BF16) { DW2_FWD_BF16 }
   if (dtype == S2LC_F32) { DW2_FWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);
@@ -881,6 +883,7 @@ int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* 
   if (s == 1) {                                          \
     if (wide) {                                          \
       if (k == 3) { if (half) DW2_B(s2lc::bf16, 3, 1, 4, 2, 2, 2, 32); DW2_B(s2lc::bf16, 3, 1, 4, 2, 2, 2, 64); } \
+      if (half5) DW2_B(s2lc::bf16, 5, 1, 4, 2, 4, 1, 32); \
       DW2_B(s2lc::bf16, 5, 1, 4, 2, 4, 1, 64);           \
     }                                                    \
     if (k == 3) DW2_B(s2lc::bf16, 3, 1, 2, 4, 2, 2, 64); \
@@ -919,6 +922,7 @@ int32_t s2lc_dwconv_bwd(const s2lc_lazygrad* g, const float* w, const s2lc_lazy*
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = W > 16;
   const bool half = W >= 64 && (((C + 63) % 64) < 32 || W >= 128 || (s2lc::debug_flags() & s2lc::DBG_DW_CB32));
+  const bool half5 = W >= 64;
   if (dtype == S2LC_BF16) { DW2_BWD_BF16 }
   if (dtype == S2LC_F32) { DW2_BWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);

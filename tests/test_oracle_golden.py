@@ -125,3 +125,18 @@ def test_oracle_training_curve(golden_meta, state_shapes):
         loss.backward()
         opt.step()
         assert abs(float(loss) - want[step]) <= 5e-4 * abs(want[step]), (step, float(loss), want[step])
+
+
+def test_trained_recipe_first_steps_follow_the_reference_curve():
+    """tests/_trained.py (the well-conditioned fixture): the oracle replays the first steps of the recipe on the CPU and
+    lands on the loss curve the LIVE reference produced (tests/golden/make_trained.py -> trained.json)."""
+    import json
+    import os
+    import _trained as T
+    want = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "trained.json")))
+    assert want["recipe"] == {"version": T.VERSION, "size": T.SIZE, "batch": T.BATCH, "steps": T.STEPS, "lr": T.LR,
+                              "weight_decay": T.WD}
+    torch.set_num_threads(max(torch.get_num_threads(), 4))
+    _, curve = T.train_oracle("cpu", steps=3)
+    for i in range(3):
+        assert abs(curve[i] - want["curve"][i]) <= 1e-4 * abs(want["curve"][i]), (i, curve[i], want["curve"][i])
