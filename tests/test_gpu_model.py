@@ -61,7 +61,10 @@ def test_b5_512_fp32_tier_b():
     assert rows[0][0] <= 1e-1, rows[:5]     # vs the fp32 oracle: bounded by mask-flip noise on both sides
 
 
-@pytest.mark.parametrize("version,size,batch", [("b0", 224, 2), ("b5", 224, 2), ("b5", 512, 1), ("b7", 1024, 1)])
+@pytest.mark.parametrize("version,size,batch", [("b0", 224, 2), ("b5", 224, 2), ("b5", 512, 1), ("b7", 1024, 1),
+                                                # BASELINE.json configs[3] at bs 4 (fp32 oracle on the GPU, TF32 off): the
+                                                # large-activation shapes of the engines (0.8 G-element tensors at bs 16)
+                                                ("b7", 1024, 4)])
 def test_bf16_within_tolerance(version, size, batch):
     """bf16 mode against the fp32 oracle, next to the reference's OWN bf16 path (torch.autocast on the GPU, what
     Lightning's precision="bf16" runs) against the same fp32 oracle.  With these random (untrained) weights the
@@ -70,7 +73,7 @@ def test_bf16_within_tolerance(version, size, batch):
     min(99.9 %, the reference's own agreement)."""
     from oracle import unet_oracle as O
     from _parity import alpha_weights
-    res = run_pair(version, size, batch, "bf16")
+    res = run_pair(version, size, batch, "bf16", oracle_device="cuda" if (version == "b7" and batch > 1) else "cpu")
     sd_c = {k: v.cuda() for k, v in res["sd"].items()}
     x, y = synthetic.tiles(batch, size).cuda(), synthetic.labels(batch, size).cuda()
     r_logits, r_loss, r_grads = O.loss_and_grads(sd_c, x, y, version, alpha=alpha_weights().cuda(), gamma=2.0,
