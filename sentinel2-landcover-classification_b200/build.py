@@ -8,7 +8,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["elementwise.cu", "igemm_simt.cu", "igemm_tc.cu", "sconv_tc.cu", "tconv_tc.cu", "twgrad_tc.cu", "swgrad_tc.cu", "wgrad_tc.cu", "conv_api.cu", "dwconv.cu", "dwconv2.cu", "stem.cu", "outconv.cu", "metrics.cu", "input.cu"]
+SOURCES = ["elementwise.cu", "igemm_simt.cu", "igemm_tc.cu", "sconv_tc.cu", "tconv_tc.cu", "twgrad_tc.cu", "swgrad_tc.cu", "wgrad_tc.cu", "conv_api.cu", "dwconv.cu", "dwconv2.cu", "dwconv2_bwd.cu", "stem.cu", "outconv.cu", "metrics.cu", "input.cu"]
 LIB = os.path.join(HERE, "libs2lc.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

@@ -52,6 +52,7 @@ uint32_t debug_flags() {
     if ((e = getenv("S2LC_TMA_ALL")) && e[0] == '1') f |= DBG_TMA_ALL;
     if ((e = getenv("S2LC_DW_CB32")) && e[0] == '1') f |= DBG_DW_CB32;
     if ((e = getenv("S2LC_NO_TMA_STORE")) && e[0] == '1') f |= DBG_NO_TMA_STORE;
+    if ((e = getenv("S2LC_DW_GENERIC")) && e[0] == '1') f |= DBG_DW_GENERIC;
     if ((e = getenv("S2LC_SWGRAD_LMAX")) && (atoi(e) == 64 || atoi(e) == 32)) f |= (uint32_t)atoi(e) << 8;
     g_dbg = f;
     g_dbg_init = true;

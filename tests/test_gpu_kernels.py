@@ -166,6 +166,74 @@ def test_dwconv_stream_plain_residual(lib, k, s, h, w, c):
     assert rel_err(dw, gw) < tol * 2
 
 
+@pytest.mark.parametrize("silu", [True, False, None])     # None: plain input WITHOUT a residual
+@pytest.mark.parametrize("k,s,n,h,w,c", [(3, 1, 3, 32, 64, 24),     # 32-channel blocks, last block 75 % full
+                                         (3, 1, 2, 32, 32, 192),    # 64-channel blocks
+                                         (5, 1, 2, 16, 64, 80),     # 5x5, 32-channel blocks
+                                         (5, 1, 2, 32, 32, 72),     # 5x5, 64-channel blocks, ragged last block
+                                         (3, 2, 2, 64, 128, 48),    # stride 2, 32-channel blocks
+                                         (3, 2, 2, 32, 32, 96),     # stride 2, 64-channel blocks
+                                         (5, 2, 2, 32, 64, 40),     # 5x5 stride 2
+                                         (3, 1, 100, 64, 64, 24),   # more strips than resident CTAs: several per CTA
+                                         (5, 1, 40, 64, 64, 136)])
+def test_dwconv_bwd_fast(lib, silu, k, s, n, h, w, c):
+    """dw2_bwdx_kernel (compile-time geometry / transforms, input tile staged by cp.async) against torch fp32 AND the
+    generic dw2_bwd_kernel on the same operands.  silu: BatchNorm + SiLU input with act' applied, lazy BatchNorm-
+    backward gradient with a per-sample rowscale; otherwise the plain input + residual of the expand-less blocks."""
+    dtype, dt, tol = DT["bf16"]
+    xr = nhwc(mk((n, c, h, w), 21), dtype)
+    xq = nchw(xr, n, h, w).requires_grad_(True)
+    wq = mk((c, 1, k, k), 22, 0.3).requires_grad_(True)
+    sc, sh = 1 + 0.1 * mk((c,), 23), 0.1 * mk((c,), 24)
+    a = F.silu(xq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1)) if silu else xq
+    ref = F.conv2d(same_pad(a, k, s), wq, stride=s, groups=c)
+    ho, wo = ref.shape[-2:]
+    dyr = nhwc(mk((n, c, ho, wo), 25), dtype)
+    zr = nhwc(mk((n, c, ho, wo), 26), dtype)
+    rs = 0.5 + torch.rand(n, device="cuda")
+    if silu:
+        p_, q_, t_ = 1 + 0.1 * mk((c,), 27), 0.05 * mk((c,), 28), 0.01 * mk((c,), 29)
+        g_ref = (p_.view(1, -1, 1, 1) * rs.view(-1, 1, 1, 1) * nchw(dyr, n, ho, wo)
+                 + q_.view(1, -1, 1, 1) * nchw(zr, n, ho, wo) + t_.view(1, -1, 1, 1))
+        lg = lazygrad(dyr, c, zr, p_, q_, t_, rs=rs)
+        lz = lazy(xr, c, sc, sh, act=1)
+        resr = None
+    else:
+        g_ref = nchw(dyr, n, ho, wo) * rs.view(-1, 1, 1, 1)
+        lg = lazygrad(dyr, c, rs=rs)
+        lz = lazy(xr, c)
+        resr = nhwc(mk((n, c, h, w), 30), dtype) if silu is False else None
+    gx, gw = torch.autograd.grad(ref, (xq, wq), g_ref)
+    want = gx / sc.view(1, -1, 1, 1) if silu else (gx + nchw(resr, n, h, w) if resr is not None else gx)
+
+    def run():
+        dx = torch.empty(n * h * w, c, dtype=dtype, device="cuda")
+        st = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+        dw = torch.zeros(c, 1, k, k, device="cuda")
+        L().check(lib.s2lc_dwconv_bwd(C.byref(lg), wq.data_ptr(), C.byref(lz), 1 if silu else 0,
+                                      resr.data_ptr() if resr is not None else None, c, dx.data_ptr(), c,
+                                      st.data_ptr(), dw.data_ptr(), n, h, w, c, k, s, dt, stream()))
+        torch.cuda.synchronize()
+        return dx, st, dw
+
+    dx, st, dw = run()
+    old = lib.s2lc_set_debug_flags(0)
+    lib.s2lc_set_debug_flags(old | 128)                   # DBG_DW_GENERIC: the generic kernel
+    try:
+        dx_g, st_g, dw_g = run()
+    finally:
+        lib.s2lc_set_debug_flags(old)
+    got = nchw(dx, n, h, w)
+    assert rel_err(got, want) < tol * 2
+    assert rel_err(dw, gw) < tol * 2
+    assert rel_err(st[:c], got.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(st[c:], (got.double() * nchw(xr, n, h, w).double()).sum((0, 2, 3))) < 1e-5
+    # same arithmetic up to the order of fp32 sums and the folded 1/2 of the tanh form
+    assert rel_err(dx.float(), dx_g.float()) < 4e-3
+    assert rel_err(dw, dw_g) < 1e-3
+    assert rel_err(st, st_g) < 1e-3
+
+
 # ----------------------------------------------------------------------------------------------- implicit GEMM
 def pack(lib, wt, dtype, dt, n1, n2, taps, c, s1, s2, st, sc, flip=False, cpad=None):
     from s2lc_b200._engine import PackedWeight
