@@ -177,6 +177,13 @@ int32_t s2lc_dwconv_fwd_tile(const s2lc_lazy* in, const float* w, void* out, dou
 int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, int32_t C, int32_t dtype, void* stream);
 int32_t s2lc_se_fc_fwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                        float* gate, int32_t N, int32_t C, int32_t S, void* stream);
+/* Allocation-free variant of s2lc_se_fc_fwd.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops).  Same arguments and
+ * results; the [N, S] hidden scratch is a static 256 KB device array (held by every GPU that loads the library until
+ * exit), so N * S <= 65536 or the call fails with S2LC_ERR_SHAPE.  It calls no cudaMalloc / cudaFree.  All calls share
+ * the array: calls that overlap on the GPU (different streams / host threads) race on it. */
+int32_t s2lc_se_fc_fwd_noalloc(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
+                               float* gate, int32_t N, int32_t C, int32_t S, void* stream);
 int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, float* dgate, int32_t N, int32_t HW,
                            int32_t C, int32_t dtype, void* stream);
 int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,

@@ -79,6 +79,7 @@ _PROTOS = {
     "s2lc_argmax_mosaic": ([vp, i64, vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, vp], i32),
     "s2lc_se_pool": ([C.POINTER(Lazy), vp, i32, i32, i32, i32, vp], i32),
     "s2lc_se_fc_fwd": ([vp, vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
+    "s2lc_se_fc_fwd_noalloc": ([vp, vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
     "s2lc_se_bwd_reduce": ([vp, i64, C.POINTER(Lazy), vp, i32, i32, i32, i32, vp], i32),
     "s2lc_se_fc_bwd": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
     "s2lc_se_bwd_apply": ([vp, i64, C.POINTER(Lazy), vp, vp, i32, i32, i32, i32, vp], i32),

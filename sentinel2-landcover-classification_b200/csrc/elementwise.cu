@@ -1062,6 +1062,39 @@ int32_t s2lc_se_fc_fwd(const float* pooled, const float* w1, const float* b1, co
   return check_launch("se_fc_fwd");
 }
 
+// ---- allocation-free variant of s2lc_se_fc_fwd (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops).  The [N, S] hidden
+// pre-activations live in a file-scope device array instead of the grown-on-demand pool above: every GPU that loads
+// the library holds these 256 KB until exit.  ALL calls share the array and it keeps the last call's contents; the
+// first kernel overwrites every element the second one reads, so nothing has to start at zero — but calls that
+// overlap on the GPU (two streams, two host threads) race on it.
+#define S2LC_SE_NOALLOC_MAX_FLOATS 65536          /* N * S <= 65536 (b7 at bs 256: 256 x 160 = 40960) */
+static __device__ __align__(256) float g_se_hp_static[S2LC_SE_NOALLOC_MAX_FLOATS];
+static float* g_se_hp_static_ptr[64];             // device address of the array, resolved once per device
+
+int32_t s2lc_se_fc_fwd_noalloc(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
+                               float* gate, int32_t N, int32_t C, int32_t S, void* stream) {
+  S2LC_REQUIRE(C % 4 == 0, S2LC_ERR_ALIGN, "se_fc_fwd_noalloc: C=%d must be a multiple of 4", C);
+  S2LC_REQUIRE(N > 0 && S > 0 && (int64_t)N * S <= S2LC_SE_NOALLOC_MAX_FLOATS, S2LC_ERR_SHAPE,
+               "se_fc_fwd_noalloc: N*S = %lld exceeds the static scratch of %d floats (use s2lc_se_fc_fwd)",
+               (long long)N * S, S2LC_SE_NOALLOC_MAX_FLOATS);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("se_fc_fwd_noalloc: bad device"); return S2LC_ERR_CUDA; }
+  if (!g_se_hp_static_ptr[dev]) {
+    // the array's name is a host-side stand-in here: the kernels need its address on the CURRENT device
+    float* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_se_hp_static);
+    if (e != cudaSuccess || !ptr) { set_error("se_fc_fwd_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return S2LC_ERR_CUDA; }
+    g_se_hp_static_ptr[dev] = ptr;
+  }
+  float* hp = g_se_hp_static_ptr[dev];
+  cudaStream_t st = (cudaStream_t)stream;
+  se_hidden_kernel<<<dim3((S + 7) / 8, N), 256, 0, st>>>(pooled, w1, b1, hp, nullptr, C, S);
+  dim3 grid((C + SE_CB - 1) / SE_CB, N);
+  se_fc_fwd_kernel<<<grid, 256, sizeof(float) * (size_t)S, st>>>(hp, w2, b2, gate, C, S);
+  return check_launch("se_fc_fwd_noalloc");
+}
+
 int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, const float* w2, const float* b2,
                        const float* dgate, float* dpool, float* dw1, float* db1, float* dw2, float* db2,
                        float* scratch, int32_t N, int32_t C, int32_t S, void* stream) {
