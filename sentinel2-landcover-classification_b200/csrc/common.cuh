@@ -26,7 +26,7 @@ int32_t check_launch(const char* what);
 int num_sms();
 // Test / profiling switches (s2lc_set_debug_flags; initialised ONCE from the environment at first use, never read
 // per launch): the defaults (0) are the product path.
-enum : uint32_t { DBG_NO_STREAM = 1u, DBG_FORCE_SIMT = 2u, DBG_SCONV_PROD7 = 4u, DBG_NO_TMA = 8u, DBG_TMA_ALL = 16u, DBG_DW_CB32 = 32u, DBG_NO_TMA_STORE = 64u, DBG_DW_GENERIC = 128u };
+enum : uint32_t { DBG_NO_STREAM = 1u, DBG_FORCE_SIMT = 2u, DBG_SCONV_PROD7 = 4u, DBG_NO_TMA = 8u, DBG_TMA_ALL = 16u, DBG_DW_CB32 = 32u, DBG_NO_TMA_STORE = 64u, DBG_DW_GENERIC = 128u, DBG_STREAM_GENERIC = 256u };
 uint32_t debug_flags();          // bits above; bits 8-15 = strip-width cap of the streaming 3x3 weight gradient (0 = none)
 #define kNumSMs (::s2lc::num_sms())
 
@@ -115,6 +115,37 @@ __device__ __forceinline__ float act_bwd_fast(float u, int act) {
   }
   if (act == S2LC_ACT_RELU) return u > 0.f ? 1.f : 0.f;
   return 1.f;
+}
+
+// packed fp32 pairs (FFMA2 / FMUL2 / FADD2: one issue slot for two lanes of math — the streaming kernels are issue-bound)
+__device__ __forceinline__ float2 f2fma(const float2& a, const float2& b, const float2& c) {  // a*b + c
+  float2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)),
+        "l"(reinterpret_cast<const unsigned long long&>(c)));
+  return d;
+}
+__device__ __forceinline__ float2 f2mul(const float2& a, const float2& b) {
+  float2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;"
+      : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 f2add(const float2& a, const float2& b) {
+  float2 d;
+  asm("add.rn.f32x2 %0, %1, %2;"
+      : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 bf2_unpack(uint32_t w) {
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+__device__ __forceinline__ uint32_t bf2_pack(const float2& v) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+  return *reinterpret_cast<uint32_t*>(&h);
 }
 
 // by storage type: bf16 -> one-MUFU forms, fp32 -> exact forms

@@ -53,6 +53,7 @@ uint32_t debug_flags() {
     if ((e = getenv("S2LC_DW_CB32")) && e[0] == '1') f |= DBG_DW_CB32;
     if ((e = getenv("S2LC_NO_TMA_STORE")) && e[0] == '1') f |= DBG_NO_TMA_STORE;
     if ((e = getenv("S2LC_DW_GENERIC")) && e[0] == '1') f |= DBG_DW_GENERIC;
+    if ((e = getenv("S2LC_STREAM_GENERIC")) && e[0] == '1') f |= DBG_STREAM_GENERIC;
     if ((e = getenv("S2LC_SWGRAD_LMAX")) && (atoi(e) == 64 || atoi(e) == 32)) f |= (uint32_t)atoi(e) << 8;
     g_dbg = f;
     g_dbg_init = true;
@@ -536,6 +537,102 @@ __global__ void __launch_bounds__(256, SE_APPLY_BLOCKS_PER_SM) se_bwd_apply_kern
   }
 }
 
+// ------------------------------------------------------------------------------------------ packed + pipelined form
+// se_bwd_apply for bf16 storage + SiLU (every squeeze-excite block of a training step): the loads of sweep i+1 are
+// issued BEFORE sweep i is consumed (register double buffer) and the math runs on packed fp32 pairs (FFMA2 / FMUL2:
+// the same operations per channel in the same order as the generic kernel, so results are bit-identical): +18 % on
+// every stage shape (profiles/r02q_stream_sweep.txt).  The same treatment was measured on se_pool / se_bwd_reduce /
+// bn_apply and did NOT pay (equal or slower: they lose more from the registers than they gain), so those stay generic.
+// act'(u) of SiLU, the packed form of act_bwd_fast
+__device__ __forceinline__ float2 dsilu2(const float2& z, const float2& sc, const float2& sh) {
+  const float2 half2 = make_float2(0.5f, 0.5f), one2 = make_float2(1.f, 1.f), mone2 = make_float2(-1.f, -1.f);
+  const float2 u = f2fma(z, sc, sh);
+  const float2 h = f2mul(u, half2);
+  const float2 s = f2fma(half2, make_float2(tanh_approx(h.x), tanh_approx(h.y)), half2);
+  return f2mul(s, f2fma(u, f2fma(s, mone2, one2), one2));
+}
+__device__ __forceinline__ uint4 ldg16(const bf16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// da <- (da*gate + dpool/HW) * act'(u), BNBWD stats against z: packed + pipelined form of se_bwd_apply_kernel
+template <int U, int MINB>
+__global__ void __launch_bounds__(256, MINB) se_bwd_apply_p_kernel(bf16* __restrict__ da, int64_t ld_da, s2lc_lazy in,
+                                                                   const float* __restrict__ dpool, double* stats,
+                                                                   int HW, int C, float inv_hw) {
+  extern __shared__ float smem[];
+  const int CV = C / 8;
+  ChanIter it(CV);
+  const int n = blockIdx.y;
+  const bf16* raw = reinterpret_cast<const bf16*>(in.raw) + (int64_t)n * HW * in.ld;
+  bf16* dap = da + (int64_t)n * HW * ld_da;
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    const int cv = cv0 + it.c_local;
+    float acc[2][8] = {};
+    if (it.active && cv < CV) {
+      float2 sc[4], sh[4], g[4], dp[4], a0[4], a1[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c = cv * 8 + 2 * i;
+        sc[i] = in.scale ? make_float2(in.scale[c], in.scale[c + 1]) : make_float2(1.f, 1.f);
+        sh[i] = in.shift ? make_float2(in.shift[c], in.shift[c + 1]) : make_float2(0.f, 0.f);
+        g[i] = in.gate ? make_float2(in.gate[(int64_t)n * C + c], in.gate[(int64_t)n * C + c + 1]) : make_float2(1.f, 1.f);
+        dp[i] = dpool ? make_float2(dpool[(int64_t)n * C + c] * inv_hw, dpool[(int64_t)n * C + c + 1] * inv_hw)
+                      : make_float2(0.f, 0.f);
+        a0[i] = a1[i] = make_float2(0.f, 0.f);
+      }
+      const int stride = gridDim.x * it.rows_par;
+      const bf16* pz = raw + cv * 8;
+      bf16* pd = dap + cv * 8;
+      uint4 cz[U], cd[U], nz[U], nd[U];
+      int r = blockIdx.x * it.rows_par + it.r_local;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int rr = r + u * stride;
+        if (rr < HW) {
+          cz[u] = ldg16(pz + (int64_t)rr * in.ld);
+          cd[u] = *reinterpret_cast<const uint4*>(pd + (int64_t)rr * ld_da);
+        }
+      }
+      for (; r < HW; r += U * stride) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {   // rows of the next sweep: never written by this sweep (distinct rows)
+          const int rr = r + (U + u) * stride;
+          if (rr < HW) {
+            nz[u] = ldg16(pz + (int64_t)rr * in.ld);
+            nd[u] = *reinterpret_cast<const uint4*>(pd + (int64_t)rr * ld_da);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int rr = r + u * stride;
+          if (rr < HW) {
+            const uint32_t zw[4] = {cz[u].x, cz[u].y, cz[u].z, cz[u].w};
+            const uint32_t dw_[4] = {cd[u].x, cd[u].y, cd[u].z, cd[u].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float2 zz = bf2_unpack(zw[i]);
+              const float2 val = f2fma(bf2_unpack(dw_[i]), g[i], dp[i]);
+              o[i] = bf2_pack(f2mul(val, dsilu2(zz, sc[i], sh[i])));
+              const float2 vr = bf2_unpack(o[i]);
+              a0[i] = f2add(a0[i], vr);
+              a1[i] = f2fma(vr, zz, a1[i]);
+            }
+            *reinterpret_cast<uint4*>(pd + (int64_t)rr * ld_da) = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) { cz[u] = nz[u]; cd[u] = nd[u]; }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[0][2 * i] = a0[i].x; acc[0][2 * i + 1] = a0[i].y;
+        acc[1][2 * i] = a1[i].x; acc[1][2 * i + 1] = a1[i].y;
+      }
+    }
+    flush_stats<2>(acc, it, cv0, C, stats, smem);
+  }
+}
+
 // ------------------------------------------------------------------------------------------ copies
 template <typename T>
 __global__ void copy_slice_kernel(const T* __restrict__ a, int64_t ld_a, const T* __restrict__ b, int64_t ld_b,
@@ -814,6 +911,139 @@ __global__ void __launch_bounds__(256) lazygrad_apply_kernel(s2lc_lazygrad g, T*
   }
 }
 
+// Streaming forms of the two kernels above for rows < 2^30 (every configuration of the reference): a thread keeps ONE
+// channel vector (per-channel constants in registers, no 64-bit division per element — the flat-index forms spend
+// ~200 instructions per 48 bytes on two emulated divisions and were issue-bound at 3.4-4.0 TB/s), rows strided over
+// the grid with U raw 16 B loads per source in flight before the first is consumed.  Same fp32 formulas, same
+// single rounding.
+template <typename T, int U>
+__global__ void __launch_bounds__(256, 3) lazygrad_apply2_kernel(s2lc_lazygrad g, T* __restrict__ out, int64_t ld_out,
+                                                              int rows, int C, int HW) {
+  const int CV = C / 8;
+  ChanIter it(CV);
+  const T* dy = reinterpret_cast<const T*>(g.dy);
+  const T* z = reinterpret_cast<const T*>(g.z);
+  const int stride = gridDim.x * it.rows_par;
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    const int cv = cv0 + it.c_local;
+    if (!it.active || cv >= CV) continue;
+    float pp[8], qq[8], tt[8];
+    if (z) {
+      Vec8<float>::load(g.p + cv * 8, pp);
+      Vec8<float>::load(g.q + cv * 8, qq);
+      Vec8<float>::load(g.t + cv * 8, tt);
+    }
+    for (int r = blockIdx.x * it.rows_par + it.r_local; r < rows; r += U * stride) {
+      RawV8<T> rd[U], rz[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int rr = r + u * stride;
+        if (rr < rows) {
+          rd[u].load(dy + (int64_t)rr * g.ld_dy + cv * 8);
+          if (z) rz[u].load(z + (int64_t)rr * g.ld_z + cv * 8);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int rr = r + u * stride;
+        if (rr < rows) {
+          float v[8];
+          rd[u].unpack(v);
+          if (g.rowscale) {
+            const float rs = __ldg(g.rowscale + rr / HW);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] *= rs;
+          }
+          if (z) {
+            float zz[8];
+            rz[u].unpack(zz);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaf(pp[j], v[j], fmaf(qq[j], zz[j], tt[j]));
+          }
+          Vec8<T>::store(out + (int64_t)rr * ld_out + cv * 8, v);
+        }
+      }
+    }
+  }
+}
+
+template <typename T, int U>
+__global__ void __launch_bounds__(256, 3) bn_apply2_kernel(s2lc_lazy in, const T* __restrict__ res, int64_t ld_res,
+                                                        const float* __restrict__ rowscale, T* __restrict__ out,
+                                                        int64_t ld_out, int rows, int C, int HW) {
+  const int CV = C / 8;
+  ChanIter it(CV);
+  const T* raw = reinterpret_cast<const T*>(in.raw);
+  const int stride = gridDim.x * it.rows_par;
+  const bool per_sample = rowscale != nullptr || in.gate != nullptr;
+  for (int cv0 = 0; cv0 < CV; cv0 += it.cvb) {
+    const int cv = cv0 + it.c_local;
+    if (!it.active || cv >= CV) continue;
+    float sc[8], sh[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = in.scale ? in.scale[cv * 8 + j] : 1.f;
+      sh[j] = in.shift ? in.shift[cv * 8 + j] : 0.f;
+    }
+    for (int r = blockIdx.x * it.rows_par + it.r_local; r < rows; r += U * stride) {
+      RawV8<T> rv[U], re[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int rr = r + u * stride;
+        if (rr < rows) {
+          rv[u].load(raw + (int64_t)rr * in.ld + cv * 8);
+          if (res) re[u].load(res + (int64_t)rr * ld_res + cv * 8);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int rr = r + u * stride;
+        if (rr < rows) {
+          const int n = per_sample ? rr / HW : 0;
+          const float rs = rowscale ? rowscale[n] : 1.f;
+          float v[8];
+          rv[u].unpack(v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = act_fwd_t<T>(v[j] * sc[j] + sh[j], in.act) * rs;
+          if (in.gate) {
+            float gt[8];
+            Vec8<float>::load(in.gate + (int64_t)n * C + cv * 8, gt);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] *= gt[j];
+          }
+          if (res) {
+            float e[8];
+            re[u].unpack(e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += e[j];
+          }
+          Vec8<T>::store(out + (int64_t)rr * ld_out + cv * 8, v);
+        }
+      }
+    }
+  }
+}
+
+// Threads per block of the ChanIter layout such that no thread idles: a multiple of the channel vectors CV = C/8
+// (<= 256), or an even split of CV when it exceeds 256.  With a fixed 256 threads C = 1056 (CV = 132) leaves 124
+// threads idle and C = 768 a quarter of them.
+static inline int chan_block(int C) {
+  const int CV = C / 8;
+  if (CV <= 256) return CV * (256 / CV);
+  const int k = (CV + 255) / 256;
+  return (CV + k - 1) / k;
+}
+// blocks of the row-strided streaming kernels: every block gets >= 2 sweeps of U rows, at most 8 blocks per SM
+static inline int stream_grid(int64_t rows, int C, int U) {
+  const int t = chan_block(C);
+  const int cvb = C / 8 < t ? C / 8 : t;
+  const int rows_par = t / cvb;
+  int64_t b = (rows + (int64_t)rows_par * U * 2 - 1) / ((int64_t)rows_par * U * 2);
+  if (b < 1) b = 1;
+  if (b > kNumSMs * 8) b = kNumSMs * 8;
+  return (int)b;
+}
+
 static inline int grid_for(int64_t work_items, int per_block, int max_blocks = kNumSMs * 8) {
   int64_t b = (work_items + per_block - 1) / per_block;
   if (b < 1) b = 1;
@@ -922,6 +1152,11 @@ int32_t s2lc_bn_apply(const s2lc_lazy* in, const void* residual, int64_t ld_res,
                       int64_t ld_out, int64_t rows, int32_t C, int32_t HW, int32_t dtype, void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_out % 8 == 0 && (!residual || ld_res % 8 == 0), S2LC_ERR_ALIGN,
                "bn_apply: C and strides must be multiples of 8 (C=%d)", C);
+  if (rows > 0 && rows < (1 << 30) && HW > 0) {
+    DISPATCH_T(dtype, (bn_apply2_kernel<T, 4><<<stream_grid(rows, C, 4), chan_block(C), 0, (cudaStream_t)stream>>>(
+                          *in, (const T*)residual, ld_res, rowscale, (T*)out, ld_out, (int)rows, C, HW)));
+    return check_launch("bn_apply");
+  }
   DISPATCH_T(dtype, (bn_apply_kernel<T><<<grid_for(rows * (C / 8), 256 * 4), 256, 0, (cudaStream_t)stream>>>(
                         *in, (const T*)residual, ld_res, rowscale, (T*)out, ld_out, rows, C, HW)));
   return check_launch("bn_apply");
@@ -949,6 +1184,11 @@ int32_t s2lc_lazygrad_apply(const s2lc_lazygrad* g, void* out, int64_t ld_out, i
   S2LC_REQUIRE(!g->z || (g->p && g->q && g->t), S2LC_ERR_SHAPE, "lazygrad_apply: z needs p, q, t");
   S2LC_REQUIRE(HW > 0, S2LC_ERR_SHAPE, "lazygrad_apply: HW");
   if (rows == 0) return S2LC_OK;
+  if (rows < (1 << 30)) {
+    DISPATCH_T(dtype, (lazygrad_apply2_kernel<T, 4><<<stream_grid(rows, C, 4), chan_block(C), 0, (cudaStream_t)stream>>>(
+                          *g, (T*)out, ld_out, (int)rows, C, HW)));
+    return check_launch("lazygrad_apply");
+  }
   DISPATCH_T(dtype, (lazygrad_apply_kernel<T><<<grid_for(rows * (C / 8), 256, kNumSMs * 8), 256, 0,
                                                 (cudaStream_t)stream>>>(*g, (T*)out, ld_out, rows, C, HW)));
   return check_launch("lazygrad_apply");
@@ -973,8 +1213,8 @@ static inline int se_vsplits(int HW, int C) {
   while (vs * 2 <= maxs && vs < 32) vs *= 2;
   return vs;
 }
-static inline int se_pool_blocks(int N, int VS) {
-  int want = (kNumSMs * SE_BLOCKS_PER_SM) / N;
+static inline int se_pool_blocks(int N, int VS, int blocks_per_sm = SE_BLOCKS_PER_SM) {
+  int want = (kNumSMs * blocks_per_sm) / N;
   int b = 1;
   while (b * 2 <= want && b * 2 <= VS) b *= 2;
   return b;
@@ -1014,7 +1254,7 @@ int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, 
   float* part; unsigned* counter;
   int32_t rc = se_scratch(N, (size_t)N * VS * C, &part, &counter);
   if (rc) return rc;
-  DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, 256, 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
+  DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, chan_block(C), 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
                         *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW, part, counter, VS)));
   return check_launch("se_pool");
 }
@@ -1027,7 +1267,7 @@ int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, f
   float* part; unsigned* counter;
   int32_t rc = se_scratch(N, (size_t)N * VS * C, &part, &counter);
   if (rc) return rc;
-  DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, 256, 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
+  DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, chan_block(C), 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
                         *in, (const T*)da, ld_da, dgate, HW, C, 1.f, part, counter, VS)));
   return check_launch("se_bwd_reduce");
 }
@@ -1116,7 +1356,14 @@ int32_t s2lc_se_bwd_apply(void* da, int64_t ld_da, const s2lc_lazy* in, const fl
                           int32_t HW, int32_t C, int32_t dtype, void* stream) {
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_da % 8 == 0, S2LC_ERR_ALIGN, "se_bwd_apply: alignment (C=%d)", C);
   dim3 grid(se_splits(N, HW, C, SE_APPLY_BLOCKS_PER_SM), N);
-  DISPATCH_T(dtype, (se_bwd_apply_kernel<T><<<grid, 256, stats_smem(C, 2), (cudaStream_t)stream>>>(
+  if (dtype == S2LC_BF16 && in->act == S2LC_ACT_SILU && !(debug_flags() & DBG_STREAM_GENERIC)) {
+    constexpr int MINB = 2;
+    grid.x = se_splits(N, HW, C, MINB);
+    se_bwd_apply_p_kernel<2, MINB><<<grid, chan_block(C), stats_smem(C, 2), (cudaStream_t)stream>>>(
+        (bf16*)da, ld_da, *in, dpool, stats, HW, C, 1.f / (float)HW);
+    return check_launch("se_bwd_apply");
+  }
+  DISPATCH_T(dtype, (se_bwd_apply_kernel<T><<<grid, chan_block(C), stats_smem(C, 2), (cudaStream_t)stream>>>(
                         (T*)da, ld_da, *in, dpool, stats, HW, C, 1.f / (float)HW)));
   return check_launch("se_bwd_apply");
 }

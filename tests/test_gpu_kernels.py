@@ -234,6 +234,36 @@ def test_dwconv_bwd_fast(lib, silu, k, s, n, h, w, c):
     assert rel_err(st, st_g) < 1e-3
 
 
+@pytest.mark.parametrize("n,hw,c", [(3, 14 * 10, 48), (2, 32 * 32, 1056), (2, 16 * 16, 3072), (4, 64 * 64, 24)])
+def test_se_bwd_apply_packed_is_bit_identical(lib, n, hw, c):
+    """se_bwd_apply_p_kernel (bf16 + SiLU: packed fp32 pairs, register double buffer) against the generic kernel on
+    the same operands: the rounded gradient must be bit-identical, the BNBWD statistics equal up to the order of
+    the atomics."""
+    dtype, dt, _ = DT["bf16"]
+    z = (mk((n * hw, c), 71) * 1.5).to(dtype)
+    da0 = mk((n * hw, c), 72).to(dtype)
+    sc, sh = 1 + 0.1 * mk((c,), 73), 0.1 * mk((c,), 74)
+    gate, dpool = torch.rand(n, c, device="cuda"), mk((n, c), 75)
+    lzg = lazy(z, c, sc, sh, gate, act=1)
+
+    def run(flags):
+        old = lib.s2lc_set_debug_flags(0)
+        lib.s2lc_set_debug_flags(old | flags)
+        try:
+            da, st = da0.clone(), torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+            L().check(lib.s2lc_se_bwd_apply(da.data_ptr(), c, C.byref(lzg), dpool.data_ptr(), st.data_ptr(), n, hw, c, dt,
+                                            stream()))
+            torch.cuda.synchronize()
+        finally:
+            lib.s2lc_set_debug_flags(old)
+        return da, st
+
+    da_p, st_p = run(0)
+    da_g, st_g = run(256)                                  # DBG_STREAM_GENERIC
+    assert torch.equal(da_p, da_g)
+    assert rel_err(st_p, st_g) < 1e-6
+
+
 # ----------------------------------------------------------------------------------------------- implicit GEMM
 def pack(lib, wt, dtype, dt, n1, n2, taps, c, s1, s2, st, sc, flip=False, cpad=None):
     from s2lc_b200._engine import PackedWeight
