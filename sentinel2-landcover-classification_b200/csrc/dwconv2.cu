@@ -46,6 +46,22 @@ using namespace s2lc;
   if (k == 3) DW2_F(float, 3, 2, 2, 2, 1, 1, 64);        \
   DW2_F(float, 5, 2, 2, 1, 1, 1, 64);
 
+// fast kernels (dw2_fwdx_kernel): bf16, exact strip geometry, input = BatchNorm + SiLU (fast == 1) or plain (fast == 2)
+#define DW2_FX(K_, S_, R_, RY_, D_, MB, CB_)                                                                    \
+  {                                                                                                             \
+    int32_t r_ = fast == 1 ? dw2::launch_fwdx<K_, S_, R_, RY_, D_, MB, CB_, true>(in, w, out, stats, N, H, W, C, st)  \
+                           : dw2::launch_fwdx<K_, S_, R_, RY_, D_, MB, CB_, false>(in, w, out, stats, N, H, W, C, st); \
+    if (r_ <= 0) return r_;                                                                                     \
+  }
+#define DW2_FWD_FAST                                     \
+  if (s == 1) {                                          \
+    if (k == 3) { if (half) DW2_FX(3, 1, 4, 4, 2, 2, 32) else DW2_FX(3, 1, 4, 4, 2, 2, 64) } \
+    else { if (half5) DW2_FX(5, 1, 4, 2, 2, 2, 32) else DW2_FX(5, 1, 4, 2, 2, 2, 64) }       \
+  } else {                                               \
+    if (k == 3) { if (half) DW2_FX(3, 2, 2, 2, 2, 2, 32) else DW2_FX(3, 2, 2, 2, 2, 2, 64) } \
+    else DW2_FX(5, 2, 2, 1, 3, 2, 64)                    \
+  }
+
 extern "C" {
 
 int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* stats, int32_t N, int32_t H, int32_t W,
@@ -58,6 +74,12 @@ int32_t s2lc_dwconv_fwd(const s2lc_lazy* in, const float* w, void* out, double* 
   // 32-channel blocks: last 64-block at most half full, or rows >= 128 px (two pixel groups per warp are 5-10 % faster there)
   const bool half = W >= 64 && (((C + 63) % 64) < 32 || W >= 128 || (s2lc::debug_flags() & s2lc::DBG_DW_CB32));
   const bool half5 = W >= 64;      // 5x5: 32-channel blocks are 5-8 % faster at 64 px rows (two pixel groups per warp)
+  int fast = 0;
+  if (dtype == S2LC_BF16 && wide && !(s2lc::debug_flags() & s2lc::DBG_DW_GENERIC)) {
+    if (in->act == S2LC_ACT_SILU && in->scale && in->shift) fast = 1;
+    if (in->act == S2LC_ACT_NONE && !in->scale && !in->shift) fast = 2;
+  }
+  if (fast) { DW2_FWD_FAST }
   if (dtype == S2LC_BF16) { DW2_FWD_BF16 }
   if (dtype == S2LC_F32) { DW2_FWD_F32 }
   s2lc::set_error("dwconv: bad dtype %d", dtype);

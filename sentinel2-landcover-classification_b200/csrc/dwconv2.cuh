@@ -824,6 +824,133 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Fast forward (bf16 storage, exact strip geometry): dw2_fwd_kernel with the launch-uniform choices made at compile
+// time — input = BatchNorm + SiLU (SILU: packed transform with pre-halved scale / shift) or a plain stored tensor, no
+// per-pixel bounds tests in the epilogue, output pointers advanced by strides.
+template <int K, int S, int R, int RY, int D, int MINB, int CB, bool SILU>
+__global__ void __launch_bounds__(NT, MINB) dw2_fwdx_kernel(s2lc_lazy in, const float* __restrict__ w,
+                                                            bf16* __restrict__ out, double* stats, Geom g) {
+  using T = bf16;
+  using Cfg = FwdCfg<T, K, S, R, RY, D, CB>;
+  using Ld = typename Cfg::Ld;
+  constexpr int WW = Cfg::WW, WIN = Cfg::WIN, NEW = Cfg::NEW, NRING = Cfg::NRING, VW = Cfg::VW, PRO = Cfg::PRO,
+                PRO_PASSES = Cfg::PRO_PASSES, NSTAGE = Cfg::NSTAGE;
+  constexpr int MODE = SILU ? 0 : 2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* tile = reinterpret_cast<float*>(smem_raw);
+  float* aux = tile + (size_t)NRING * WW * CB;  // [2][CB] scale / 2, shift / 2 (SILU) or 1, 0
+  float* sstat = aux + 2 * CB;                   // [2][CB]
+  unsigned char* stages = reinterpret_cast<unsigned char*>(sstat + 2 * CB);
+  constexpr int HL = CB / 2, NH = Cfg::NH;
+  const int lane = (threadIdx.x & 31) % HL, pg = (threadIdx.x >> 5) * NH + (threadIdx.x & 31) / HL;
+  const int cb0 = blockIdx.y * CB;
+  const int c = cb0 + 2 * lane;
+  const bool cvalid = c < g.C;
+  if (threadIdx.x < CB) {
+    const int cc = cb0 + threadIdx.x;
+    aux[threadIdx.x] = SILU ? 0.5f * (cc < g.C ? in.scale[cc] : 1.f) : 1.f;
+    aux[CB + threadIdx.x] = SILU ? 0.5f * (cc < g.C ? in.shift[cc] : 0.f) : 0.f;
+  }
+  if (threadIdx.x < 2 * CB) sstat[threadIdx.x] = 0.f;
+  float2 wr[K * K];
+#pragma unroll
+  for (int t = 0; t < K * K; ++t)
+    wr[t] = cvalid ? make_float2(w[(int64_t)c * K * K + t], w[(int64_t)(c + 1) * K * K + t]) : make_float2(0.f, 0.f);
+  float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
+  const T* src = reinterpret_cast<const T*>(in.raw);
+  Ld ld;
+  const int items = g.N * g.ychunks * g.xs;
+  const int nsteps = g.YC / RY;                       // exact geometry
+  const int64_t orow = (int64_t)g.Wd * g.C;
+  int iss = 0, com = 0;
+  auto next = [](int& x) { int r = x; x = (x + 1 == NSTAGE) ? 0 : x + 1; return r; };
+  const float2 one2 = make_float2(1.f, 1.f);
+
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int n = item / (g.ychunks * g.xs);
+    const int rem = item - n * g.ychunks * g.xs;
+    const int y0 = (rem / g.xs) * g.YC, x0 = (rem % g.xs) * Cfg::TW;
+    const int gy0 = y0 * S - g.pad_t, gx0 = x0 * S - g.pad_l;
+    ld.begin_item(src, in.ld, src, in.ld, n, g.Hs, g.Ws, gy0, gx0, cb0, g.C);
+    auto issue = [&](int rel0, int nr) { ld.issue(stages + (size_t)next(iss) * Ld::STAGE_BYTES, rel0, nr); };
+    T* op = out + (((int64_t)n * g.Hd + y0) * g.Wd + x0 + pg * R) * g.C + c;   // advanced by RY rows per step
+#pragma unroll
+    for (int pp = 0; pp < PRO_PASSES; ++pp) issue(pp * NEW, min(NEW, PRO - pp * NEW));
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      if (d < nsteps) issue(PRO + d * NEW, NEW);
+      else cp_async_commit();
+    }
+    cp_async_wait<D - 1>();
+    __syncthreads();  // previous item's readers are done with the ring; aux/sstat initialised
+#pragma unroll
+    for (int pp = 0; pp < PRO_PASSES; ++pp)
+      ld.template commit_ct<MODE, true>(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux, pp * NEW,
+                                        (pp * NEW) % NRING, min(NEW, PRO - pp * NEW));
+    ld.template commit_ct<MODE, false>(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux, PRO, PRO % NRING, NEW);
+    int cslot = (PRO + NEW) % NRING;
+    __syncthreads();
+    int base = 0;
+    for (int t = 0; t < nsteps; ++t) {
+      if (t + D < nsteps) issue(PRO + (t + D) * NEW, NEW);
+      else cp_async_commit();
+      float2 acc[RY][R];
+#pragma unroll
+      for (int dy = 0; dy < RY; ++dy)
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[dy][r] = make_float2(0.f, 0.f);
+      const float* tl = tile + (pg * R * S) * CB + 2 * lane;
+#pragma unroll
+      for (int j = 0; j < WIN; ++j) {
+        int slot = base + j;
+        if (slot >= NRING) slot -= NRING;
+        const float* rp = tl + (size_t)slot * WW * CB;
+        float2 v[VW];
+#pragma unroll
+        for (int i = 0; i < VW; ++i) v[i] = *reinterpret_cast<const float2*>(rp + i * CB);
+#pragma unroll
+        for (int dy = 0; dy < RY; ++dy) {
+          const int ky = j - dy * S;
+          if (ky < 0 || ky >= K) continue;
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int kx = 0; kx < K; ++kx) ffma2(acc[dy][r], wr[ky * K + kx], v[r * S + kx]);
+        }
+      }
+      if (cvalid) {
+#pragma unroll
+        for (int dy = 0; dy < RY; ++dy) {
+          T* opr = op + dy * orow;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const float2 ab = st_pair_rt<T>(opr + r * g.C, acc[dy][r]);   // stored (rounded) values
+            ffma2(s0, ab, one2);
+            ffma2(s1, ab, ab);
+          }
+        }
+      }
+      op += RY * orow;
+      base += NEW;
+      if (base >= NRING) base -= NRING;
+      if (t + 1 < nsteps) {
+        cp_async_wait<D - 1>();
+        __syncthreads();
+        ld.template commit_ct<MODE, false>(stages + (size_t)next(com) * Ld::STAGE_BYTES, tile, aux,
+                                           PRO + (t + 1) * NEW, cslot, NEW);
+        cslot += NEW;
+        if (cslot >= NRING) cslot -= NRING;
+        __syncthreads();
+      }
+    }
+  }
+  if (stats) {
+    __syncthreads();
+    flush_stats<CB>(s0, s1, sstat, cb0, g.C, stats);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Fast fused backward (bf16 storage, the shapes of the b5 / b7 encoders): same algorithm and ring as dw2_bwd_kernel
 // with everything that is uniform over a launch resolved at compile time — the strip geometry divides the image (no
 // per-pixel bounds tests), the input transform is either BatchNorm + SiLU with act' applied (SILU) or a plain stored
@@ -1218,6 +1345,32 @@ static int32_t launch_bwd(const s2lc_lazygrad* gin, const float* w, const s2lc_l
   kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*gin, w, *in, apply_act_bwd, (const T*)res, ld_res, (T*)out, ld_out,
                                                  stats, dw, g);
   return check_launch("dwconv2_bwd");
+}
+
+// fast forward: returns 1 when the geometry is not exact (the caller then uses the generic kernel)
+template <int K, int S, int R, int RY, int D, int MINB, int CB, bool SILU>
+static int32_t launch_fwdx(const s2lc_lazy* in, const float* w, void* out, double* stats, int N, int H, int W, int C,
+                           cudaStream_t st) {
+  using Cfg = FwdCfg<bf16, K, S, R, RY, D, CB>;
+  auto kern = dw2_fwdx_kernel<K, S, R, RY, D, MINB, CB, SILU>;
+  Geom g{};
+  g.N = N; g.C = C; g.Hs = H; g.Ws = W;
+  g.Hd = (H + S - 1) / S; g.Wd = (W + S - 1) / S;
+  int ph = (g.Hd - 1) * S + K - H; if (ph < 0) ph = 0;
+  int pw = (g.Wd - 1) * S + K - W; if (pw < 0) pw = 0;
+  g.pad_t = ph / 2; g.pad_l = pw / 2;
+  const int cblocks = (C + CB - 1) / CB;
+  int32_t r = set_smem(kern, Cfg::SMEM);
+  if (r) return r;
+  static int resident = resident_ctas(kern, Cfg::SMEM);
+  plan_strips(g, Cfg::TW, RY, cblocks, resident);
+  if (g.Wd % Cfg::TW != 0 || g.Hd % g.YC != 0 || g.YC % RY != 0) return 1;
+  long items = (long)g.N * g.xs * g.ychunks;
+  int gx = resident / cblocks;
+  if (gx < 1) gx = 1;
+  if (gx > items) gx = (int)items;
+  kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*in, w, (bf16*)out, stats, g);
+  return check_launch("dwconv2_fwdx");
 }
 
 // fast variant: returns 1 when the geometry is not exact (the caller then uses the generic kernel)

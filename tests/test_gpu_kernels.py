@@ -264,6 +264,45 @@ def test_se_bwd_apply_packed_is_bit_identical(lib, n, hw, c):
     assert rel_err(st_p, st_g) < 1e-6
 
 
+@pytest.mark.parametrize("silu", [True, False])
+@pytest.mark.parametrize("k,s,n,h,w,c", [(3, 1, 3, 32, 64, 24), (3, 1, 2, 32, 32, 192), (5, 1, 2, 16, 64, 80),
+                                         (5, 1, 2, 32, 32, 72), (3, 2, 2, 64, 128, 48), (3, 2, 2, 64, 64, 96),
+                                         (5, 2, 2, 32, 64, 40), (3, 1, 100, 64, 64, 24), (5, 1, 40, 64, 64, 136)])
+def test_dwconv_fwd_fast(lib, silu, k, s, n, h, w, c):
+    """dw2_fwdx_kernel (compile-time geometry / transform) against torch fp32 and the generic dw2_fwd_kernel."""
+    dtype, dt, tol = DT["bf16"]
+    xr = nhwc(mk((n, c, h, w), 41), dtype)
+    xq = nchw(xr, n, h, w)
+    wq = mk((c, 1, k, k), 42, 0.3)
+    sc, sh = 1 + 0.1 * mk((c,), 43), 0.1 * mk((c,), 44)
+    a = F.silu(xq * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1)) if silu else xq
+    ref = F.conv2d(same_pad(a, k, s), wq, stride=s, groups=c)
+    ho, wo = ref.shape[-2:]
+    lz = lazy(xr, c, sc, sh, act=1) if silu else lazy(xr, c)
+
+    def run(flags):
+        old = lib.s2lc_set_debug_flags(0)
+        lib.s2lc_set_debug_flags(old | flags)
+        try:
+            out = torch.empty(n * ho * wo, c, dtype=dtype, device="cuda")
+            st = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+            L().check(lib.s2lc_dwconv_fwd(C.byref(lz), wq.data_ptr(), out.data_ptr(), st.data_ptr(), n, h, w, c, k, s, dt,
+                                          stream()))
+            torch.cuda.synchronize()
+        finally:
+            lib.s2lc_set_debug_flags(old)
+        return out, st
+
+    out, st = run(0)
+    out_g, st_g = run(128)                                # DBG_DW_GENERIC
+    got = nchw(out, n, ho, wo)
+    assert rel_err(got, ref) < tol
+    assert rel_err(st[:c], got.double().sum((0, 2, 3))) < 1e-5
+    assert rel_err(st[c:], (got.double() ** 2).sum((0, 2, 3))) < 1e-5
+    assert rel_err(out.float(), out_g.float()) < 4e-3
+    assert rel_err(st, st_g) < 1e-3
+
+
 # ----------------------------------------------------------------------------------------------- implicit GEMM
 def pack(lib, wt, dtype, dt, n1, n2, taps, c, s1, s2, st, sc, flip=False, cpad=None):
     from s2lc_b200._engine import PackedWeight
