@@ -30,8 +30,9 @@ TMA_OPERANDS = os.environ.get("S2LC_NO_TMA", "0") != "1"
 
 
 # MBConv blocks up to this many pixels per sample get their project-conv operand / BatchNorm-backward gradients
-# materialised (A/B knob: S2LC_TMA_BLOCK_HW; 128 x 128 measured 0.8 ms per step better than 64 x 64, 256 x 256 is a loss)
-TMA_BLOCK_HW = int(os.environ.get("S2LC_TMA_BLOCK_HW", str(128 * 128)))
+# materialised (A/B knob: S2LC_TMA_BLOCK_HW; 128 x 128 measured 0.8 ms per step better than 64 x 64; 256 x 256 was a loss
+# until the materialisation passes reached 3.7-5.8 TB/s and is 0.3 ms better since: profiles/r02s_bench_hw256.json)
+TMA_BLOCK_HW = int(os.environ.get("S2LC_TMA_BLOCK_HW", str(256 * 256)))
 
 
 def tma_takes_3x3(width: int, c: int) -> bool:

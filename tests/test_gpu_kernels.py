@@ -303,6 +303,35 @@ def test_dwconv_fwd_fast(lib, silu, k, s, n, h, w, c):
     assert rel_err(st, st_g) < 1e-3
 
 
+@pytest.mark.parametrize("ratio,bound", [(1.0, 1e-5), (10.0, 2e-4), (100.0, 2e-2)])
+def test_batchnorm_moments_with_large_mean(lib, ratio, bound):
+    """the producers accumulate one-pass moments (sum, sum of squares; fp32 per thread, fp64 across
+    threads), so var = E[x^2] - mean^2 loses (mean/std)^2 of the fp32 partial-sum accuracy.  Measured here on the
+    depthwise forward (fp32 storage, so the stored values are exact) for |mean|/std = 1, 10, 100 and bounded; BatchNorm
+    inputs in this network are conv outputs with |mean|/std of order 1 (tests/test_gpu_trained.py runs the flat bars
+    on trained weights)."""
+    n, c, h, w, k = 8, 64, 64, 64, 3
+    x = ratio + mk((n, c, h, w), 91)
+    wt = torch.zeros(c, 1, k, k, device="cuda")
+    wt[:, 0, 1, 1] = 1.0                                    # identity stencil: out == in away from nothing (centre tap)
+    xr = nhwc(x, torch.float32)
+    out = torch.empty(n * h * w, c, device="cuda")
+    stats = torch.zeros(2 * c, dtype=torch.float64, device="cuda")
+    lz = lazy(xr, c)
+    L().check(lib.s2lc_dwconv_fwd(C.byref(lz), wt.data_ptr(), out.data_ptr(), stats.data_ptr(), n, h, w, c, k, 1, 0,
+                                  stream()))
+    torch.cuda.synchronize()
+    cnt = n * h * w
+    mean = stats[:c] / cnt
+    var = stats[c:] / cnt - mean * mean
+    o = out.double()
+    var_ref = o.var(0, unbiased=False)
+    err = float(((var - var_ref).abs() / var_ref).max())
+    print(f"\n[moments |mean|/std = {ratio:g}] worst relative error of the batch variance: {err:.2e}")
+    assert float(((mean - o.mean(0)).abs() / o.mean(0).abs().clamp_min(1e-3)).max()) < 1e-6
+    assert err < bound
+
+
 # ----------------------------------------------------------------------------------------------- implicit GEMM
 def pack(lib, wt, dtype, dt, n1, n2, taps, c, s1, s2, st, sc, flip=False, cpad=None):
     from s2lc_b200._engine import PackedWeight

@@ -66,3 +66,9 @@ for name, idx in (("ref32", 1), ("ours32", 2), ("oursbf", 3), ("refbf", 4)):
 well = [r for r in rows if r[1] <= 1e-5]
 print("tensors with ref32-vs-64 <= 1e-5:", len(well), "of", len(rows), "; of those ours32 <= 1e-4:", sum(r[2] <= 1e-4 for r in well),
       "worst ours32 on them %.2e" % max((r[2] for r in well), default=0.0))
+for r in sorted(well, key=lambda r: -r[2]):
+    print(f"  well {r[0]:45s} ref32 {r[1]:.1e} ours32 {r[2]:.1e}")
+print("decoder tensors (ref32 / ours32):")
+for r in rows:
+    if not r[0].startswith("encoder."):
+        print(f"  {r[0]:45s} {r[1]:.1e} {r[2]:.1e}  |g| {float(g64[r[0]].norm()):.2e}")
