@@ -128,6 +128,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ stats, const float
                                    float* running_mean, float* running_var, float* scale, float* shift, float* mean_o,
                                    float* invstd_o, int C) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
+  cudaGridDependencySynchronize();   // launched programmatically dependent: the producers' statistics are complete
   if (c >= C) return;
   double mean = stats[c] / count;
   double var = stats[C + c] / count - mean * mean;
@@ -158,6 +159,7 @@ __global__ void bn_bwd_finalize_kernel(const double* __restrict__ stats, const f
                                        const float* __restrict__ invstd, const float* __restrict__ gamma, double count,
                                        float* p, float* q, float* t, float* dgamma, float* dbeta, int C) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
+  cudaGridDependencySynchronize();
   if (c >= C) return;
   // stats[c] = sum dy, stats[C+c] = sum dy*z  ->  sum dy*zhat = r*(sum dy z - mu*sum dy)
   double sdy = stats[c], sdyz = stats[C + c];
@@ -368,6 +370,7 @@ constexpr int SE_CB = 256;
 __global__ void __launch_bounds__(256) se_hidden_kernel(const float* __restrict__ pooled, const float* __restrict__ w1,
                                                         const float* __restrict__ b1, float* __restrict__ hp,
                                                         float* __restrict__ zero, int C, int S) {
+  cudaGridDependencySynchronize();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.y, s = blockIdx.x * 8 + warp;
   if (s >= S) return;
@@ -389,6 +392,7 @@ __global__ void __launch_bounds__(256) se_hidden_kernel(const float* __restrict_
 __global__ void __launch_bounds__(256) se_fc_fwd_kernel(const float* __restrict__ hp, const float* __restrict__ w2,
                                                         const float* __restrict__ b2, float* __restrict__ gate, int C,
                                                         int S) {
+  cudaGridDependencySynchronize();
   extern __shared__ float smem[];
   float* hs = smem;  // [S]
   const int n = blockIdx.y, c = blockIdx.x * SE_CB + threadIdx.x;
@@ -408,6 +412,7 @@ __global__ void __launch_bounds__(256) se_fc_bwd1_kernel(const float* __restrict
                                                          const float* __restrict__ dgate, float* __restrict__ sc_dgp,
                                                          const float* __restrict__ sc_hp, float* __restrict__ sc_dacc,
                                                          int C, int S) {
+  cudaGridDependencySynchronize();
   extern __shared__ float smem[];
   float* hs = smem;               // [S] silu(hp)
   float* dg = hs + S;             // [SE_CB]
@@ -439,6 +444,7 @@ __global__ void __launch_bounds__(256) se_fc_bwd1_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) se_fc_bwd2_kernel(const float* __restrict__ w1, const float* __restrict__ sc_hp,
                                                          const float* __restrict__ sc_dacc, float* __restrict__ dpool,
                                                          int C, int S) {
+  cudaGridDependencySynchronize();
   extern __shared__ float smem[];
   float* dh = smem;  // [S]
   const int n = blockIdx.y, c = blockIdx.x * SE_CB + threadIdx.x;
@@ -463,6 +469,7 @@ __global__ void __launch_bounds__(256) se_fc_bwd_weight_kernel(const float* __re
                                                                float* __restrict__ dw1, float* __restrict__ db1,
                                                                float* __restrict__ dw2, float* __restrict__ db2, int N,
                                                                int C, int S) {
+  cudaGridDependencySynchronize();
   extern __shared__ float smem[];
   float* sh = smem;       // [N] silu(hp[n, s])
   float* dh = smem + N;   // [N] dacc[n, s] * silu'(hp[n, s])
@@ -1065,6 +1072,20 @@ static inline int grid_for(int64_t work_items, int per_block, int max_blocks = k
 
 using namespace s2lc;
 
+static cudaLaunchAttribute g_pdl_attr;
+static inline cudaLaunchConfig_t pdl_config(dim3 grid, int block, cudaStream_t st, size_t smem = 0) {
+  g_pdl_attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  g_pdl_attr.val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cfg.attrs = &g_pdl_attr;
+  cfg.numAttrs = 1;
+  return cfg;
+}
+
 #define DISPATCH_T(dtype, ...)                                   \
   if ((dtype) == S2LC_F32) {                                     \
     typedef float T;                                             \
@@ -1136,9 +1157,11 @@ int32_t s2lc_weight_pack(const float* src, void* dst, int32_t dtype, int32_t N1,
 int32_t s2lc_bn_finalize(const double* stats, const float* gamma, const float* beta, double count, float eps,
                          float momentum, float* running_mean, float* running_var, float* scale, float* shift,
                          float* mean, float* invstd, int32_t C, void* stream) {
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, gamma, beta, count, eps, momentum,
-                                                                         running_mean, running_var, scale, shift,
-                                                                         mean, invstd, C);
+  // programmatic dependent launch: these [C]-sized kernels are pure launch latency (252 of them per training step);
+  // their grid is scheduled while the producer of the statistics drains and waits in cudaGridDependencySynchronize()
+  cudaLaunchConfig_t cfg = pdl_config(dim3((C + 127) / 128), 128, (cudaStream_t)stream);
+  cudaLaunchKernelEx(&cfg, bn_finalize_kernel, stats, gamma, beta, count, eps, momentum, running_mean, running_var, scale,
+                     shift, mean, invstd, (int)C);
   return check_launch("bn_finalize");
 }
 
@@ -1153,8 +1176,8 @@ int32_t s2lc_bn_eval_affine(const float* gamma, const float* beta, const float* 
 int32_t s2lc_bn_bwd_finalize(const double* stats, const float* mean, const float* invstd, const float* gamma,
                              double count, float* p, float* q, float* t, float* dgamma, float* dbeta, int32_t C,
                              void* stream) {
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, mean, invstd, gamma, count, p, q,
-                                                                             t, dgamma, dbeta, C);
+  cudaLaunchConfig_t cfg = pdl_config(dim3((C + 127) / 128), 128, (cudaStream_t)stream);
+  cudaLaunchKernelEx(&cfg, bn_bwd_finalize_kernel, stats, mean, invstd, gamma, count, p, q, t, dgamma, dbeta, (int)C);
   return check_launch("bn_bwd_finalize");
 }
 
@@ -1306,9 +1329,11 @@ int32_t s2lc_se_fc_fwd(const float* pooled, const float* w1, const float* b1, co
   int32_t rc = se_hp_scratch((size_t)N * S, &hp);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  se_hidden_kernel<<<dim3((S + 7) / 8, N), 256, 0, st>>>(pooled, w1, b1, hp, nullptr, C, S);
-  dim3 grid((C + SE_CB - 1) / SE_CB, N);
-  se_fc_fwd_kernel<<<grid, 256, sizeof(float) * (size_t)S, st>>>(hp, w2, b2, gate, C, S);
+  float* nozero = nullptr;
+  cudaLaunchConfig_t c1 = pdl_config(dim3((S + 7) / 8, N), 256, st);
+  cudaLaunchKernelEx(&c1, se_hidden_kernel, pooled, w1, b1, hp, nozero, (int)C, (int)S);
+  cudaLaunchConfig_t c2 = pdl_config(dim3((C + SE_CB - 1) / SE_CB, N), 256, st, sizeof(float) * (size_t)S);
+  cudaLaunchKernelEx(&c2, se_fc_fwd_kernel, (const float*)hp, w2, b2, gate, (int)C, (int)S);
   return check_launch("se_fc_fwd");
 }
 
@@ -1354,12 +1379,16 @@ int32_t s2lc_se_fc_bwd(const float* pooled, const float* w1, const float* b1, co
   float* sc_hp = scratch + (size_t)N * C;        // [N, S] hidden pre-activation
   float* sc_dacc = sc_hp + (size_t)N * S;        // [N, S] sum_c dgp * W2 (accumulated atomically)
   cudaStream_t st = (cudaStream_t)stream;
-  se_hidden_kernel<<<dim3((S + 7) / 8, N), 256, 0, st>>>(pooled, w1, b1, sc_hp, sc_dacc, C, S);
-  dim3 grid((C + SE_CB - 1) / SE_CB, N);
-  se_fc_bwd1_kernel<<<grid, 256, sizeof(float) * (size_t)(S + SE_CB), st>>>(w2, b2, dgate, sc_dgp, sc_hp, sc_dacc, C, S);
-  se_fc_bwd2_kernel<<<grid, 256, sizeof(float) * (size_t)S, st>>>(w1, sc_hp, sc_dacc, dpool, C, S);
-  se_fc_bwd_weight_kernel<<<dim3((C + SE_CB - 1) / SE_CB, S), 256, sizeof(float) * 2 * (size_t)N, st>>>(
-      pooled, sc_dgp, sc_hp, sc_dacc, dw1, db1, dw2, db2, N, C, S);
+  const dim3 grid((C + SE_CB - 1) / SE_CB, N);
+  cudaLaunchConfig_t c0 = pdl_config(dim3((S + 7) / 8, N), 256, st);
+  cudaLaunchKernelEx(&c0, se_hidden_kernel, pooled, w1, b1, sc_hp, sc_dacc, (int)C, (int)S);
+  cudaLaunchConfig_t c1 = pdl_config(grid, 256, st, sizeof(float) * (size_t)(S + SE_CB));
+  cudaLaunchKernelEx(&c1, se_fc_bwd1_kernel, w2, b2, dgate, sc_dgp, (const float*)sc_hp, sc_dacc, (int)C, (int)S);
+  cudaLaunchConfig_t c2 = pdl_config(grid, 256, st, sizeof(float) * (size_t)S);
+  cudaLaunchKernelEx(&c2, se_fc_bwd2_kernel, w1, (const float*)sc_hp, (const float*)sc_dacc, dpool, (int)C, (int)S);
+  cudaLaunchConfig_t c3 = pdl_config(dim3((C + SE_CB - 1) / SE_CB, S), 256, st, sizeof(float) * 2 * (size_t)N);
+  cudaLaunchKernelEx(&c3, se_fc_bwd_weight_kernel, pooled, (const float*)sc_dgp, (const float*)sc_hp,
+                     (const float*)sc_dacc, dw1, db1, dw2, db2, (int)N, (int)C, (int)S);
   return check_launch("se_fc_bwd");
 }
 
