@@ -459,6 +459,7 @@ struct FwdCfg {
 template <typename T, int K, int S, int R, int RY, int D, int MINB, int CB>
 __global__ void __launch_bounds__(NT, MINB) dw2_fwd_kernel(s2lc_lazy in, const float* __restrict__ w,
                                                            T* __restrict__ out, double* stats, Geom g) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   using Cfg = FwdCfg<T, K, S, R, RY, D, CB>;
   using Ld = typename Cfg::Ld;
   constexpr int WW = Cfg::WW, WIN = Cfg::WIN, NEW = Cfg::NEW, NRING = Cfg::NRING, VW = Cfg::VW, PRO = Cfg::PRO,
@@ -612,6 +613,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
                                                            const T* __restrict__ res, int64_t ld_res,
                                                            T* __restrict__ out, int64_t ld_out, double* stats,
                                                            float* __restrict__ dw, Geom g) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   using Cfg = BwdCfg<T, K, S, R, RY, D, CB>;
   using Ld = typename Cfg::Ld;
   constexpr bool FAST = sizeof(T) == 2;
@@ -830,6 +832,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwd_kernel(s2lc_lazygrad gin, co
 template <int K, int S, int R, int RY, int D, int MINB, int CB, bool SILU>
 __global__ void __launch_bounds__(NT, MINB) dw2_fwdx_kernel(s2lc_lazy in, const float* __restrict__ w,
                                                             bf16* __restrict__ out, double* stats, Geom g) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   using T = bf16;
   using Cfg = FwdCfg<T, K, S, R, RY, D, CB>;
   using Ld = typename Cfg::Ld;
@@ -993,6 +996,7 @@ __global__ void __launch_bounds__(NT, MINB) dw2_bwdx_kernel(s2lc_lazygrad gin, c
                                                             s2lc_lazy in, const bf16* __restrict__ res,
                                                             int64_t ld_res, bf16* __restrict__ out, int64_t ld_out,
                                                             double* stats, float* __restrict__ dw, Geom g) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   using T = bf16;
   using X = BwdxCfg<K, S, R, RY, D, CB, ONEBAR>;
   using Ld = typename X::Ld;
@@ -1319,7 +1323,7 @@ static int32_t launch_fwd(const s2lc_lazy* in, const float* w, void* out, double
   int gx = resident / cblocks;   // never more CTAs than are co-resident: a partial second wave doubles the time
   if (gx < 1) gx = 1;
   if (gx > items) gx = (int)items;
-  kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*in, w, (T*)out, stats, g);
+  PDL_LAUNCH(kern, dim3(gx, cblocks), NT, Cfg::SMEM, st, *in, w, (T*)out, stats, g);
   return check_launch("dwconv2_fwd");
 }
 
@@ -1342,8 +1346,8 @@ static int32_t launch_bwd(const s2lc_lazygrad* gin, const float* w, const s2lc_l
   int gx = resident / cblocks;   // never more CTAs than are co-resident: a partial second wave doubles the time
   if (gx < 1) gx = 1;
   if (gx > items) gx = (int)items;
-  kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*gin, w, *in, apply_act_bwd, (const T*)res, ld_res, (T*)out, ld_out,
-                                                 stats, dw, g);
+  PDL_LAUNCH(kern, dim3(gx, cblocks), NT, Cfg::SMEM, st, *gin, w, *in, (int)apply_act_bwd, (const T*)res, ld_res, (T*)out,
+             ld_out, stats, dw, g);
   return check_launch("dwconv2_bwd");
 }
 
@@ -1369,7 +1373,7 @@ static int32_t launch_fwdx(const s2lc_lazy* in, const float* w, void* out, doubl
   int gx = resident / cblocks;
   if (gx < 1) gx = 1;
   if (gx > items) gx = (int)items;
-  kern<<<dim3(gx, cblocks), NT, Cfg::SMEM, st>>>(*in, w, (bf16*)out, stats, g);
+  PDL_LAUNCH(kern, dim3(gx, cblocks), NT, Cfg::SMEM, st, *in, w, (bf16*)out, stats, g);
   return check_launch("dwconv2_fwdx");
 }
 
@@ -1395,8 +1399,8 @@ static int32_t launch_bwdx(const s2lc_lazygrad* gin, const float* w, const s2lc_
   int gx = resident / cblocks;
   if (gx < 1) gx = 1;
   if (gx > items) gx = (int)items;
-  kern<<<dim3(gx, cblocks), NT, X::SMEM, st>>>(*gin, w, *in, (const bf16*)res, ld_res, (bf16*)out, ld_out, stats, dw,
-                                               g);
+  PDL_LAUNCH(kern, dim3(gx, cblocks), NT, X::SMEM, st, *gin, w, *in, (const bf16*)res, ld_res, (bf16*)out, ld_out, stats,
+             dw, g);
   return check_launch("dwconv2_bwdx");
 }
 

@@ -275,6 +275,7 @@ constexpr int SE_APPLY_BLOCKS_PER_SM = 3;   // se_bwd_apply holds 4 per-channel 
 template <typename T, bool WITH_DA>
 __global__ void __launch_bounds__(256, SE_BLOCKS_PER_SM) se_pool_kernel(s2lc_lazy in, const T* __restrict__ da, int64_t ld_da, float* __restrict__ out, int HW,
                                int C, float mul, float* __restrict__ part, unsigned* __restrict__ counter, int VS) {
+  cudaGridDependencySynchronize();
   // grid: (blocks per sample, N).  WITH_DA: out[n,c] = sum da*act(u)  (d gate), else mean of act(u).
   // The rows of a sample are dealt to VS VIRTUAL splits, VS a function of (HW, C) only; a block walks the virtual
   // splits blockIdx.x, blockIdx.x + gridDim.x, ...  Every partial therefore sums the same rows in the same order
@@ -499,6 +500,7 @@ __global__ void __launch_bounds__(256) se_fc_bwd_weight_kernel(const float* __re
 template <typename T>
 __global__ void __launch_bounds__(256, SE_APPLY_BLOCKS_PER_SM) se_bwd_apply_kernel(T* __restrict__ da, int64_t ld_da, s2lc_lazy in, const float* __restrict__ dpool,
                                     double* stats, int HW, int C, float inv_hw) {
+  cudaGridDependencySynchronize();
   extern __shared__ float smem[];
   const int CV = C / 8;
   ChanIter it(CV);
@@ -575,6 +577,7 @@ template <int U, int MINB>
 __global__ void __launch_bounds__(256, MINB) se_bwd_apply_p_kernel(bf16* __restrict__ da, int64_t ld_da, s2lc_lazy in,
                                                                    const float* __restrict__ dpool, double* stats,
                                                                    int HW, int C, float inv_hw) {
+  cudaGridDependencySynchronize();
   extern __shared__ float smem[];
   const int CV = C / 8;
   ChanIter it(CV);
@@ -936,6 +939,7 @@ __global__ void __launch_bounds__(256) lazygrad_apply_kernel(s2lc_lazygrad g, T*
 template <typename T, int U>
 __global__ void __launch_bounds__(256, 3) lazygrad_apply2_kernel(s2lc_lazygrad g, T* __restrict__ out, int64_t ld_out,
                                                               int rows, int C, int HW) {
+  cudaGridDependencySynchronize();
   const int CV = C / 8;
   ChanIter it(CV);
   const T* dy = reinterpret_cast<const T*>(g.dy);
@@ -988,6 +992,7 @@ template <typename T, int U>
 __global__ void __launch_bounds__(256, 3) bn_apply2_kernel(s2lc_lazy in, const T* __restrict__ res, int64_t ld_res,
                                                         const float* __restrict__ rowscale, T* __restrict__ out,
                                                         int64_t ld_out, int rows, int C, int HW) {
+  cudaGridDependencySynchronize();
   const int CV = C / 8;
   ChanIter it(CV);
   const T* raw = reinterpret_cast<const T*>(in.raw);
@@ -1071,20 +1076,6 @@ static inline int grid_for(int64_t work_items, int per_block, int max_blocks = k
 }  // namespace s2lc
 
 using namespace s2lc;
-
-static cudaLaunchAttribute g_pdl_attr;
-static inline cudaLaunchConfig_t pdl_config(dim3 grid, int block, cudaStream_t st, size_t smem = 0) {
-  g_pdl_attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  g_pdl_attr.val.programmaticStreamSerializationAllowed = 1;
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = grid;
-  cfg.blockDim = dim3(block);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cfg.attrs = &g_pdl_attr;
-  cfg.numAttrs = 1;
-  return cfg;
-}
 
 #define DISPATCH_T(dtype, ...)                                   \
   if ((dtype) == S2LC_F32) {                                     \
@@ -1186,8 +1177,9 @@ int32_t s2lc_bn_apply(const s2lc_lazy* in, const void* residual, int64_t ld_res,
   S2LC_REQUIRE(C % 8 == 0 && in->ld % 8 == 0 && ld_out % 8 == 0 && (!residual || ld_res % 8 == 0), S2LC_ERR_ALIGN,
                "bn_apply: C and strides must be multiples of 8 (C=%d)", C);
   if (rows > 0 && rows < (1 << 30) && HW > 0) {
-    DISPATCH_T(dtype, (bn_apply2_kernel<T, 4><<<stream_grid(rows, C, 4), chan_block(C), 0, (cudaStream_t)stream>>>(
-                          *in, (const T*)residual, ld_res, rowscale, (T*)out, ld_out, (int)rows, C, HW)));
+    DISPATCH_T(dtype, PDL_LAUNCH((bn_apply2_kernel<T, 4>), dim3(stream_grid(rows, C, 4)), chan_block(C), 0,
+                                 (cudaStream_t)stream, *in, (const T*)residual, ld_res, rowscale, (T*)out, ld_out,
+                                 (int)rows, (int)C, (int)HW));
     return check_launch("bn_apply");
   }
   DISPATCH_T(dtype, (bn_apply_kernel<T><<<grid_for(rows * (C / 8), 256 * 4), 256, 0, (cudaStream_t)stream>>>(
@@ -1218,8 +1210,8 @@ int32_t s2lc_lazygrad_apply(const s2lc_lazygrad* g, void* out, int64_t ld_out, i
   S2LC_REQUIRE(HW > 0, S2LC_ERR_SHAPE, "lazygrad_apply: HW");
   if (rows == 0) return S2LC_OK;
   if (rows < (1 << 30)) {
-    DISPATCH_T(dtype, (lazygrad_apply2_kernel<T, 4><<<stream_grid(rows, C, 4), chan_block(C), 0, (cudaStream_t)stream>>>(
-                          *g, (T*)out, ld_out, (int)rows, C, HW)));
+    DISPATCH_T(dtype, PDL_LAUNCH((lazygrad_apply2_kernel<T, 4>), dim3(stream_grid(rows, C, 4)), chan_block(C), 0,
+                                 (cudaStream_t)stream, *g, (T*)out, ld_out, (int)rows, (int)C, (int)HW));
     return check_launch("lazygrad_apply");
   }
   DISPATCH_T(dtype, (lazygrad_apply_kernel<T><<<grid_for(rows * (C / 8), 256, kNumSMs * 8), 256, 0,
@@ -1287,8 +1279,9 @@ int32_t s2lc_se_pool(const s2lc_lazy* in, float* pooled, int32_t N, int32_t HW, 
   float* part; unsigned* counter;
   int32_t rc = se_scratch(N, (size_t)N * VS * C, &part, &counter);
   if (rc) return rc;
-  DISPATCH_T(dtype, (se_pool_kernel<T, false><<<grid, chan_block(C), 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
-                        *in, nullptr, 0, pooled, HW, C, 1.f / (float)HW, part, counter, VS)));
+  DISPATCH_T(dtype, PDL_LAUNCH((se_pool_kernel<T, false>), grid, chan_block(C), 256 * 8 * sizeof(float),
+                               (cudaStream_t)stream, *in, (const T*)nullptr, (int64_t)0, pooled, (int)HW, (int)C,
+                               1.f / (float)HW, part, counter, VS));
   return check_launch("se_pool");
 }
 
@@ -1300,8 +1293,9 @@ int32_t s2lc_se_bwd_reduce(const void* da, int64_t ld_da, const s2lc_lazy* in, f
   float* part; unsigned* counter;
   int32_t rc = se_scratch(N, (size_t)N * VS * C, &part, &counter);
   if (rc) return rc;
-  DISPATCH_T(dtype, (se_pool_kernel<T, true><<<grid, chan_block(C), 256 * 8 * sizeof(float), (cudaStream_t)stream>>>(
-                        *in, (const T*)da, ld_da, dgate, HW, C, 1.f, part, counter, VS)));
+  DISPATCH_T(dtype, PDL_LAUNCH((se_pool_kernel<T, true>), grid, chan_block(C), 256 * 8 * sizeof(float),
+                               (cudaStream_t)stream, *in, (const T*)da, ld_da, dgate, (int)HW, (int)C, 1.f, part, counter,
+                               VS));
   return check_launch("se_bwd_reduce");
 }
 
@@ -1399,12 +1393,12 @@ int32_t s2lc_se_bwd_apply(void* da, int64_t ld_da, const s2lc_lazy* in, const fl
   if (dtype == S2LC_BF16 && in->act == S2LC_ACT_SILU && !(debug_flags() & DBG_STREAM_GENERIC)) {
     constexpr int MINB = 2;
     grid.x = se_splits(N, HW, C, MINB);
-    se_bwd_apply_p_kernel<2, MINB><<<grid, chan_block(C), stats_smem(C, 2), (cudaStream_t)stream>>>(
-        (bf16*)da, ld_da, *in, dpool, stats, HW, C, 1.f / (float)HW);
+    PDL_LAUNCH((se_bwd_apply_p_kernel<2, MINB>), grid, chan_block(C), stats_smem(C, 2), (cudaStream_t)stream, (bf16*)da,
+               ld_da, *in, dpool, stats, (int)HW, (int)C, 1.f / (float)HW);
     return check_launch("se_bwd_apply");
   }
-  DISPATCH_T(dtype, (se_bwd_apply_kernel<T><<<grid, chan_block(C), stats_smem(C, 2), (cudaStream_t)stream>>>(
-                        (T*)da, ld_da, *in, dpool, stats, HW, C, 1.f / (float)HW)));
+  DISPATCH_T(dtype, PDL_LAUNCH((se_bwd_apply_kernel<T>), grid, chan_block(C), stats_smem(C, 2), (cudaStream_t)stream,
+                               (T*)da, ld_da, *in, dpool, stats, (int)HW, (int)C, 1.f / (float)HW));
   return check_launch("se_bwd_apply");
 }
 

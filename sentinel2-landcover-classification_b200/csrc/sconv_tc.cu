@@ -109,6 +109,7 @@ struct SCursor {
 // across tiles and are reduced over the warp only when they are flushed.
 template <int TAPS, bool REGSTAT>
 __global__ void __launch_bounds__(SC_THREADS, 1) sconv_kernel(ConvArgs P, SPlan K) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -732,7 +733,7 @@ int32_t launch_sconv_tc(const ConvArgs& A, cudaStream_t st) {
     }
     attr_set = true;
   }
-  kern<<<ctas * K.nsplit, SC_THREADS, smem, st>>>(A, K);
+  PDL_LAUNCH(kern, dim3(ctas * K.nsplit), SC_THREADS, smem, st, A, K);
   return check_launch("sconv_tc");
 }
 

@@ -95,6 +95,7 @@ struct WCursor {
 
 template <int TAPS, bool CT>   // CT: 2x2 transposed conv (1x1 path with strided gradient rows, four children)
 __global__ void __launch_bounds__(SW_THREADS, 1) swgrad_kernel(WgradArgs P, WPlan K) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -622,9 +623,9 @@ int32_t launch_swgrad_tc(const WgradArgs& A, cudaStream_t st) {
     }
     attr_set = true;
   }
-  if (K.taps == 9) swgrad_kernel<9, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
-  else if (children == 4) swgrad_kernel<1, true><<<ctas * K.nsplit * K.children, SW_THREADS, smem, st>>>(A, K);
-  else swgrad_kernel<1, false><<<ctas * K.nsplit, SW_THREADS, smem, st>>>(A, K);
+  if (K.taps == 9) PDL_LAUNCH((swgrad_kernel<9, false>), dim3(ctas * K.nsplit), SW_THREADS, smem, st, A, K);
+  else if (children == 4) PDL_LAUNCH((swgrad_kernel<1, true>), dim3(ctas * K.nsplit * K.children), SW_THREADS, smem, st, A, K);
+  else PDL_LAUNCH((swgrad_kernel<1, false>), dim3(ctas * K.nsplit), SW_THREADS, smem, st, A, K);
   return check_launch("swgrad_tc");
 }
 

@@ -117,6 +117,7 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 __global__ void __launch_bounds__(TV_THREADS, 1) tconv_kernel(ConvArgs P, TPlan K, const __grid_constant__ CUtensorMap tmA,
                                                               const __grid_constant__ CUtensorMap tmB,
                                                               const __grid_constant__ CUtensorMap tmO) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -724,7 +725,7 @@ int32_t launch_tconv_tc(const ConvArgs& A, cudaStream_t st) {
     attr_set = true;
   }
   int grid = kNumSMs < K.total_tiles ? kNumSMs : K.total_tiles;
-  tconv_kernel<<<grid, TV_THREADS, smem, st>>>(A, K, tmA, tmB, tmO);
+  PDL_LAUNCH(tconv_kernel, dim3(grid), TV_THREADS, smem, st, A, K, tmA, tmB, tmO);
   note_tma_launch();
   return check_launch("tconv_tc");
 }

@@ -87,6 +87,7 @@ __device__ __forceinline__ GItem item_of(const GPlan& K, int it) {
 __global__ void __launch_bounds__(TG_THREADS, 1) twgrad_kernel(WgradArgs P, GPlan K,
                                                                const __grid_constant__ CUtensorMap tmA,
                                                                const __grid_constant__ CUtensorMap tmG) {
+  cudaGridDependencySynchronize();   // programmatic dependent launch (common.cuh)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -445,7 +446,7 @@ int32_t launch_twgrad_tc(const WgradArgs& A, cudaStream_t st) {
   }
   if (A.dbias) launch_colsum_bf16(A.g.dy, A.g.ld_dy, M * (K.kind == 2 ? 4 : 1), A.Cout, A.dbias, st);
   const int grid = sms < K.items ? sms : K.items;
-  twgrad_kernel<<<grid, TG_THREADS, smem, st>>>(A, K, tmA, tmG);
+  PDL_LAUNCH(twgrad_kernel, dim3(grid), TG_THREADS, smem, st, A, K, tmA, tmG);
   note_tma_launch();
   return check_launch("twgrad_tc");
 }
