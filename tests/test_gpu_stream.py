@@ -96,7 +96,7 @@ def test_stream_conv1x1(lib, cin, cout, n, h, w, gated):
     # data gradient cout -> cin with drop-connect row scale, residual, act'(prev), BNBWD statistics
     dy, z = mk((rows, cout), 116).to(BF), mk((rows, cout), 117).to(BF)
     p_, q_, t_ = 1 + 0.1 * mk((cout,), 118), 0.05 * mk((cout,), 119), 0.01 * mk((cout,), 120)
-    rsc = 0.5 + torch.rand(n, device="cuda")
+    rsc = 0.5 + torch.sigmoid(torch.randn(n, generator=torch.Generator(device="cuda").manual_seed(97), device="cuda"))
     lg = L().LazyGrad(dy.data_ptr(), cout, z.data_ptr(), cout, p_.data_ptr(), q_.data_ptr(), t_.data_ptr(), rsc.data_ptr())
     pwd = pack(lib, wt, BF, 1, 1, cin, 1, cout, 0, 1, 0, cin)
     res = mk((rows, cin), 121).to(BF)
@@ -157,7 +157,7 @@ def test_stream_wgrad1x1(lib, cin, cout, n, h, w, gated):
     lz = lazy(x, cin, sc, sh, gate, act=1)
     dy, z = mk((rows, cout), 145).to(BF), mk((rows, cout), 146).to(BF)
     p_, q_, t_ = 1 + 0.1 * mk((cout,), 147), 0.05 * mk((cout,), 148), 0.01 * mk((cout,), 149)
-    rsc = 0.5 + torch.rand(n, device="cuda")
+    rsc = 0.5 + torch.sigmoid(torch.randn(n, generator=torch.Generator(device="cuda").manual_seed(97), device="cuda"))
     lg = L().LazyGrad(dy.data_ptr(), cout, z.data_ptr(), cout, p_.data_ptr(), q_.data_ptr(), t_.data_ptr(), rsc.data_ptr())
     (rw, _), (gw, _) = _both(lambda: _run_wgrad(lib, 0, lz, lg, n, h, w, cin, cout, (cout, cin, 1, 1), False))
     assert rel_err(gw, rw) < 1e-3

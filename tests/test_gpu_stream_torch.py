@@ -140,7 +140,7 @@ def test_conv1x1_vs_torch(lib, cin, cout, n, h, w, gated):
     # data gradient cout -> cin with drop-connect row scale, residual, act'(prev), BNBWD statistics
     dy, z = mk((rows, cout), 216).to(BF), mk((rows, cout), 217).to(BF)
     p_, q_, t_ = 1 + 0.1 * mk((cout,), 218), 0.05 * mk((cout,), 219), 0.01 * mk((cout,), 220)
-    rsc = 0.5 + torch.rand(n, device="cuda")
+    rsc = 0.5 + torch.sigmoid(torch.randn(n, generator=torch.Generator(device="cuda").manual_seed(97), device="cuda"))
     lg = L().LazyGrad(dy.data_ptr(), cout, z.data_ptr(), cout, p_.data_ptr(), q_.data_ptr(), t_.data_ptr(), rsc.data_ptr())
     pwd = pack(lib, wt, BF, 1, 1, cin, 1, cout, 0, 1, 0, cin)
     res = mk((rows, cin), 221).to(BF)
@@ -195,7 +195,7 @@ def test_wgrad1x1_vs_torch(lib, cin, cout, n, h, w, gated):
     gate = torch.sigmoid(mk((n, cin), 244)) if gated else None
     dy, z = mk((rows, cout), 245).to(BF), mk((rows, cout), 246).to(BF)
     p_, q_, t_ = 1 + 0.1 * mk((cout,), 247), 0.05 * mk((cout,), 248), 0.01 * mk((cout,), 249)
-    rsc = 0.5 + torch.rand(n, device="cuda")
+    rsc = 0.5 + torch.sigmoid(torch.randn(n, generator=torch.Generator(device="cuda").manual_seed(97), device="cuda"))
     lg = L().LazyGrad(dy.data_ptr(), cout, z.data_ptr(), cout, p_.data_ptr(), q_.data_ptr(), t_.data_ptr(), rsc.data_ptr())
     dw = torch.zeros(cout, cin, 1, 1, device="cuda")
     run_wgrad(lib, 1, 0, lazy(x, cin, sc, sh, gate, act=1), lg, n, h, w, cin, cout, dw)
