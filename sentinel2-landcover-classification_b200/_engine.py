@@ -104,6 +104,7 @@ class Engine:
         self._pack_sig: dict[torch.dtype, tuple] = {}
         self._param_ptrs = self._ptr_signature()
         self.weight_gen = 0        # bumped by every out-of-band parameter update (FusedAdam writes through raw pointers)
+        self.stats_gen = 0         # bumped by every training-mode forward (BatchNorm running statistics change)
         self.packs_version = 0     # bumped whenever a packed weight is added (FusedAdam rebuilds its table)
         self.direct_grad = False   # DataParallelTrainer: leave grads in flat_grad instead of returning clones
         self.timing_hook = None    # {"fwd": [], "bwd": [], "only": {kernel-class labels}} — see Workspace.run_forward
@@ -197,6 +198,9 @@ class Workspace:
         self.x_ptr = C.c_void_p(0)
         self.dlogits_ptr_holder: L.LazyGrad | None = None
         self.n_bn_trained: list[torch.Tensor] = []
+        self.affine_list: list[tuple] = []          # eval mode: the s2lc_bn_eval_affine launches (see bn_forward)
+        self._affine_buffers: list[torch.Tensor] = []
+        self._affine_sig: tuple | None = None
         self._build()
 
     # ---------------------------------------------------------------- allocation helpers
@@ -330,8 +334,13 @@ class Workspace:
                    bn.shift.data_ptr(), bn.mean.data_ptr(), bn.invstd.data_ptr(), bn.C)
             self.n_bn_trained.append(m.num_batches_tracked)
         else:
-            self.F("s2lc_bn_eval_affine", m.weight.data_ptr(), m.bias.data_ptr(), m.running_mean.data_ptr(),
-                   m.running_var.data_ptr(), float(m.eps), bn.scale.data_ptr(), bn.shift.data_ptr(), bn.C)
+            # eval mode: scale / shift depend on parameters and running statistics only — computed once and again only
+            # when those change (run_forward), not 126 times per forward
+            self.affine_list.append((self.lib.s2lc_bn_eval_affine,
+                                     (m.weight.data_ptr(), m.bias.data_ptr(), m.running_mean.data_ptr(),
+                                      m.running_var.data_ptr(), float(m.eps), bn.scale.data_ptr(), bn.shift.data_ptr(),
+                                      bn.C)))
+            self._affine_buffers += [m.running_mean, m.running_var]
 
     def bn_backward(self, bn: _BN, key: str) -> None:
         m = bn.mod
@@ -805,7 +814,17 @@ class Workspace:
         self.x_ptr.value = x.data_ptr()
         if self.training:
             L.check(lib.s2lc_memset_zero(self.stats_f_arena.data_ptr(), self.stats_f_arena.numel() * 8, st))
+            self.eng.stats_gen += 1          # running statistics are about to change (written through raw pointers)
         self.eng.repack(self.dtype, st)
+        if self.affine_list:
+            sig = (self.eng.weight_signature(), self.eng.stats_gen, sum(b._version for b in self._affine_buffers),
+                   hash(tuple(b.data_ptr() for b in self._affine_buffers)))
+            if sig != self._affine_sig:
+                for fn, args in self.affine_list:
+                    rc = fn(*args, st)
+                    if rc:
+                        L.check(rc)
+                self._affine_sig = sig
         if events is None and self.eng.timing_hook is not None:
             events, only = self.eng.timing_hook["fwd"], self.eng.timing_hook["only"]
         for i, (fn, args) in enumerate(self.fwd_list):

@@ -244,3 +244,38 @@ def test_reference_segmentation_module_drop_in():
     loss = module._model_step(batch, "train")
     loss.backward()
     assert torch.isfinite(loss)
+
+
+def test_eval_affine_coefficients_follow_the_buffers():
+    """Eval mode computes the BatchNorm scale / shift vectors once per workspace and again only when a parameter or a
+    running statistic changed: in-place edits of a buffer, a training forward (which updates the running statistics
+    through raw pointers) and an optimizer-free weight edit must all be picked up by the next eval forward."""
+    from oracle import unet_oracle as O
+    model, sd = build_model("b0", "fp32")
+    x = synthetic.tiles(2, 64).cuda()
+
+    def ours_eval():
+        model.eval()
+        with torch.no_grad():
+            return model(x).float().clone()
+
+    def oracle_eval():
+        cur = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        return O.unet_forward(cur, x, "b0", training=False).float()
+
+    o1 = ours_eval()
+    assert rel(o1, oracle_eval()) <= 1e-4
+    assert torch.equal(ours_eval(), o1)                                # cached coefficients: same result
+    with torch.no_grad():                                              # (1) a buffer edited in place
+        model.encoder.stem[1].running_var.mul_(1.7)
+        model.double_convs[0][1].running_mean.add_(0.05)
+    o2 = ours_eval()
+    assert not torch.equal(o2, o1) and rel(o2, oracle_eval()) <= 1e-4
+    model.train()                                                      # (2) a training forward moves the statistics
+    model(x)
+    o3 = ours_eval()
+    assert not torch.equal(o3, o2) and rel(o3, oracle_eval()) <= 1e-4
+    with torch.no_grad():                                              # (3) a BatchNorm weight edited in place
+        model.encoder.stem[1].weight.mul_(0.9)
+    o4 = ours_eval()
+    assert not torch.equal(o4, o3) and rel(o4, oracle_eval()) <= 1e-4
