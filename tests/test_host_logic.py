@@ -99,6 +99,14 @@ def test_engine_dry_run_builds_launch_lists():
     # just require positive, finite metadata on every conv launch)
     for label, nbytes, flops, desc in ws.fwd_meta + ws.bwd_meta:
         assert nbytes >= 0 and flops >= 0
+    # eval mode: the BatchNorm scale / shift launches sit in their own list (run once per parameter / running-statistic
+    # state, Workspace.run_forward), one per BatchNorm layer the forward uses, and not in the per-call forward list
+    ws_e = eng.workspace(x, torch.bfloat16, False, False)
+    n_bn = sum(1 for m in model.modules() if isinstance(m, torch.nn.BatchNorm2d))
+    assert 0 < len(ws_e.affine_list) <= n_bn and len(ws_e._affine_buffers) == 2 * len(ws_e.affine_list)
+    assert not ws.affine_list                                        # training mode computes batch statistics instead
+    assert all(meta[0] != "bn_eval_affine" for meta in ws_e.fwd_meta)
+    assert len(ws_e.fwd_list) == len(ws_e.fwd_meta)
 
 
 def test_bucket_schedule_covers_every_bucket_once():
