@@ -295,7 +295,9 @@ int64_t s2lc_tma_launches(int32_t reset);
 /* SM count of the current device (sizes every persistent grid; read once from the driver, not a constant). */
 int32_t s2lc_num_sms(void);
 /* Test / profiling switches (bit 0: no streaming engines, 1: force the CUDA-core engine, 2: 7 producer warps,
- * 3: no TMA feed; bits 8-15: strip-width cap of the streaming 3x3 weight gradient).  Returns the previous value.
+ * 3: no TMA feed, 4: TMA engines take every plain shape, 5: 32-channel depthwise blocks everywhere, 6: no TMA-store
+ * epilogue, 7: generic depthwise kernels instead of the fast ones, 16: generic squeeze-excite backward kernel instead of
+ * the packed one; bits 8-15: strip-width cap of the streaming 3x3 weight gradient, from S2LC_SWGRAD_LMAX).  Returns the previous value.
  * Initialised once from S2LC_* environment variables; the default 0 is the product path. */
 uint32_t s2lc_set_debug_flags(uint32_t flags);
 

@@ -26,7 +26,7 @@ int32_t check_launch(const char* what);
 int num_sms();
 // Test / profiling switches (s2lc_set_debug_flags; initialised ONCE from the environment at first use, never read
 // per launch): the defaults (0) are the product path.
-enum : uint32_t { DBG_NO_STREAM = 1u, DBG_FORCE_SIMT = 2u, DBG_SCONV_PROD7 = 4u, DBG_NO_TMA = 8u, DBG_TMA_ALL = 16u, DBG_DW_CB32 = 32u, DBG_NO_TMA_STORE = 64u, DBG_DW_GENERIC = 128u, DBG_STREAM_GENERIC = 256u };
+enum : uint32_t { DBG_NO_STREAM = 1u, DBG_FORCE_SIMT = 2u, DBG_SCONV_PROD7 = 4u, DBG_NO_TMA = 8u, DBG_TMA_ALL = 16u, DBG_DW_CB32 = 32u, DBG_NO_TMA_STORE = 64u, DBG_DW_GENERIC = 128u, DBG_STREAM_GENERIC = 1u << 16 /* bits 8-15 are the strip-width cap */ };
 uint32_t debug_flags();          // bits above; bits 8-15 = strip-width cap of the streaming 3x3 weight gradient (0 = none)
 #define kNumSMs (::s2lc::num_sms())
 

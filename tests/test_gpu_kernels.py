@@ -259,7 +259,7 @@ def test_se_bwd_apply_packed_is_bit_identical(lib, n, hw, c):
         return da, st
 
     da_p, st_p = run(0)
-    da_g, st_g = run(256)                                  # DBG_STREAM_GENERIC
+    da_g, st_g = run(1 << 16)                              # DBG_STREAM_GENERIC
     assert torch.equal(da_p, da_g)
     assert rel_err(st_p, st_g) < 1e-6
 
